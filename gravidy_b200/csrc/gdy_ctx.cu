@@ -1,0 +1,901 @@
+// gdy_ctx.cu — the context behind include/gravidy_b200.h: device memory, launch logic, NCCL plumbing
+// and the C ABI itself.  sm_100a only; there is no CPU path in this file or anywhere in the library.
+//
+// One gdy_ctx = one GPU = one j-shard.  State is replicated on every shard; the force kernels of a
+// shard see the j-tiles [tile_begin, tile_end) only, and the partial forces of the (shared) active list
+// are summed over the shards with ncclAllReduce (reference's equivalent: the host loop
+// h_f[id] += h_fout_gpu[g][i], src/include/gpu/Hermite4GPU.cu:512-530; MPI back end:
+// src/include/mpi/Hermite4MPI.cpp:202).
+#include "../../include/gravidy_b200.h"
+#include "gdy_force.cuh"
+#include "gdy_step.cuh"
+
+#include <chrono>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <dlfcn.h>
+#include <nccl.h>   // types only; the library is bound with dlopen so that a process which already
+                    // carries an NCCL (e.g. torch's bundled one) shares it instead of loading a second.
+#include <vector>
+
+using namespace gdy;
+
+// ---- NCCL, bound at run time ---------------------------------------------------------------------------
+namespace {
+struct NcclApi
+{
+    void *h = nullptr;
+    ncclResult_t (*GetUniqueId)(ncclUniqueId *) = nullptr;
+    ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*AllReduce)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t,
+                              cudaStream_t) = nullptr;
+    const char *(*GetErrorString)(ncclResult_t) = nullptr;
+    bool ok = false;
+};
+NcclApi g_nccl;
+char g_create_err[512] = "";
+
+bool nccl_load()
+{
+    if (g_nccl.ok) return true;
+    const char *names[] = {"libnccl.so.2", "libnccl.so"};
+    for (const char *nm : names)
+    {
+        g_nccl.h = dlopen(nm, RTLD_NOW | RTLD_GLOBAL);
+        if (g_nccl.h) break;
+    }
+    if (!g_nccl.h) return false;
+#define GDY_SYM(field, name) \
+    *(void **)(&g_nccl.field) = dlsym(g_nccl.h, name); \
+    if (!g_nccl.field) return false;
+    GDY_SYM(GetUniqueId, "ncclGetUniqueId")
+    GDY_SYM(CommInitRank, "ncclCommInitRank")
+    GDY_SYM(CommDestroy, "ncclCommDestroy")
+    GDY_SYM(AllReduce, "ncclAllReduce")
+    GDY_SYM(GetErrorString, "ncclGetErrorString")
+#undef GDY_SYM
+    g_nccl.ok = true;
+    return true;
+}
+}  // namespace
+
+// ---- the context ---------------------------------------------------------------------------------------
+struct gdy_ctx
+{
+    int device = 0, rank = 0, world = 1;
+    uint32_t n = 0, npad = 0;
+    double e2 = 0.0;
+    float eta = 0.0f;
+    bool mask_self = false;          // e2 == 0: the self pair must be masked
+    cudaStream_t st = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    ncclComm_t comm = nullptr;
+
+    double *pool = nullptr;          // every double array of State lives here
+    size_t pool_doubles = 0;
+    State s{};
+    uint32_t *d_move = nullptr;      // s.move
+    uint32_t *d_ilist = nullptr;     // explicit list for gdy_force_sweep
+    uint32_t *d_block_cnt = nullptr;
+    uint32_t n_sched_blocks = 0;
+    double *d_block_min = nullptr;
+    uint32_t n_min_blocks = 0;
+    SchedOut *d_sched = nullptr;
+    double *d_atime = nullptr;
+    double *d_energy = nullptr;      // [2]
+    double *d_stage = nullptr;       // AoS staging, npad*8 doubles
+    size_t part_cap = 0;             // doubles in s.part
+
+    struct Pinned { SchedOut sched; double atime; double energy[2]; } *pin = nullptr;
+
+    uint32_t tile_begin = 0, tile_end = 0;   // this shard's j-tiles (units of TJ)
+    int num_sms = 148;
+    int tune_variant = -1, tune_jsplit = -1;
+    uint32_t seq = 0;
+    uint32_t last_nact = 0;
+    bool have_particles = false, have_pred = false;
+    uint64_t launches = 0;
+    double force_ms_acc = 0.0;
+    char err[512] = "";
+};
+
+namespace {
+
+int fail(gdy_ctx *c, int code, const char *fmt, ...)
+{
+    char *dst = c ? c->err : g_create_err;
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(dst, 512, fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+#define CU(call) \
+    do { \
+        cudaError_t e_ = (call); \
+        if (e_ != cudaSuccess) \
+            return fail(c, GDY_ERR_CUDA, "%s:%d %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); \
+    } while (0)
+
+#define NC(call) \
+    do { \
+        ncclResult_t r_ = (call); \
+        if (r_ != ncclSuccess) \
+            return fail(c, GDY_ERR_NCCL, "%s:%d %s: %s", __FILE__, __LINE__, #call, g_nccl.GetErrorString(r_)); \
+    } while (0)
+
+#define LAUNCHED(c) \
+    do { \
+        ++(c)->launches; \
+        CU(cudaGetLastError()); \
+    } while (0)
+
+inline uint32_t cdiv(uint32_t a, uint32_t b) { return (a + b - 1) / b; }
+inline uint32_t round_up(uint32_t a, uint32_t b) { return cdiv(a, b) * b; }
+
+int bind_device(gdy_ctx *c) { CU(cudaSetDevice(c->device)); return 0; }
+#define BIND(c) do { int r_ = bind_device(c); if (r_) return r_; } while (0)
+
+}  // namespace
+
+// ---- lifetime ------------------------------------------------------------------------------------------
+extern "C" int gdy_abi_version(void) { return 1; }
+
+extern "C" const char *gdy_last_error(const gdy_ctx *c) { return c ? c->err : g_create_err; }
+
+extern "C" int gdy_nccl_unique_id(uint8_t *uid_out)
+{
+    gdy_ctx *c = nullptr;
+    if (!uid_out) return fail(c, GDY_ERR_INVALID, "uid_out is NULL");
+    if (!nccl_load()) return fail(c, GDY_ERR_NCCL, "libnccl.so.2 not loadable: %s", dlerror());
+    static_assert(sizeof(ncclUniqueId) == GDY_NCCL_UID_BYTES, "ncclUniqueId size");
+    ncclUniqueId id;
+    NC(g_nccl.GetUniqueId(&id));
+    memcpy(uid_out, &id, sizeof id);
+    return GDY_OK;
+}
+
+namespace {
+
+constexpr size_t PART_MIN_DOUBLES = (size_t)8 << 20;   // 64 MiB of j-split partials at least
+
+int alloc_all(gdy_ctx *c)
+{
+    const size_t np = c->npad;
+    // 7 (r,m,v) + 6 f + 6 old + 3 a2 + 3 a3 + 2 (t,dt) + 6 p + 6 ip + 6 fsum
+    const size_t narr = 7 + 6 + 6 + 3 + 3 + 2 + 6 + 6 + 6;
+    c->part_cap = 6 * np > PART_MIN_DOUBLES ? 6 * np : PART_MIN_DOUBLES;
+    c->pool_doubles = narr * np + c->part_cap;
+    CU(cudaMalloc(&c->pool, c->pool_doubles * sizeof(double)));
+    CU(cudaMemsetAsync(c->pool, 0, c->pool_doubles * sizeof(double), c->st));
+    double *q = c->pool;
+    auto take = [&](size_t cnt) { double *r = q; q += cnt; return r; };
+    State &s = c->s;
+    s.x = take(np); s.y = take(np); s.z = take(np); s.m = take(np);
+    s.vx = take(np); s.vy = take(np); s.vz = take(np);
+    for (int k = 0; k < 6; ++k) s.f[k] = take(np);
+    for (int k = 0; k < 6; ++k) s.old[k] = take(np);
+    for (int k = 0; k < 3; ++k) s.a2[k] = take(np);
+    for (int k = 0; k < 3; ++k) s.a3[k] = take(np);
+    s.t = take(np); s.dt = take(np);
+    for (int k = 0; k < 6; ++k) s.p[k] = take(np);
+    for (int k = 0; k < 6; ++k) s.ip[k] = take(np);
+    s.fsum = take(6 * np);
+    s.part = take(c->part_cap);
+
+    CU(cudaMalloc(&c->d_move, np * sizeof(uint32_t)));
+    CU(cudaMemsetAsync(c->d_move, 0xFF, np * sizeof(uint32_t), c->st));
+    s.move = c->d_move;
+    CU(cudaMalloc(&c->d_ilist, np * sizeof(uint32_t)));
+    c->n_sched_blocks = cdiv(c->n, SCHED_CHUNK);
+    CU(cudaMalloc(&c->d_block_cnt, c->n_sched_blocks * sizeof(uint32_t)));
+    c->n_min_blocks = cdiv(c->n, 256 * 4);
+    if (c->n_min_blocks > (uint32_t)MIN_BLOCKS) c->n_min_blocks = MIN_BLOCKS;
+    CU(cudaMalloc(&c->d_block_min, MIN_BLOCKS * sizeof(double)));
+    CU(cudaMalloc(&c->d_sched, sizeof(SchedOut)));
+    CU(cudaMalloc(&c->d_atime, sizeof(double)));
+    CU(cudaMalloc(&c->d_energy, 2 * sizeof(double)));
+    CU(cudaMalloc(&c->d_stage, np * 8 * sizeof(double)));
+    CU(cudaHostAlloc(&c->pin, sizeof(*c->pin), cudaHostAllocDefault));
+    memset(c->pin, 0, sizeof(*c->pin));
+
+    // padding particles: zero mass, far away, at rest (they contribute exactly 0 to every sum)
+    const uint32_t npd = c->npad - c->n;
+    if (npd)
+    {
+        double *far[6] = {s.x, s.y, s.z, s.p[0], s.p[1], s.p[2]};
+        for (double *a : far)
+        {
+            k_fill<<<cdiv(npd, 256), 256, 0, c->st>>>(a, PAD_POS, c->n, c->npad);
+            LAUNCHED(c);
+        }
+    }
+    CU(cudaStreamSynchronize(c->st));
+    return 0;
+}
+
+}  // namespace
+
+extern "C" int gdy_create_sharded(gdy_ctx **out, uint32_t n, double e2, float eta, int device, int rank,
+                                  int world, const uint8_t *nccl_uid)
+{
+    gdy_ctx *c = nullptr;
+    if (!out) return fail(c, GDY_ERR_INVALID, "out is NULL");
+    *out = nullptr;
+    if (n == 0) return fail(c, GDY_ERR_INVALID, "n must be > 0");
+    if (!(e2 >= 0.0)) return fail(c, GDY_ERR_INVALID, "e2 must be >= 0");
+    if (world < 1 || rank < 0 || rank >= world) return fail(c, GDY_ERR_INVALID, "bad rank/world %d/%d", rank, world);
+    if (world > 1 && !nccl_uid) return fail(c, GDY_ERR_INVALID, "world > 1 needs an NCCL unique id");
+    int ndev = 0;
+    cudaError_t ce = cudaGetDeviceCount(&ndev);
+    if (ce != cudaSuccess || ndev == 0)
+        return fail(c, GDY_ERR_NO_DEVICE, "no CUDA device (%s); gravidy_b200 has no CPU path",
+                    ce == cudaSuccess ? "device count 0" : cudaGetErrorString(ce));
+    if (device < 0 || device >= ndev) return fail(c, GDY_ERR_INVALID, "device %d out of range (%d devices)", device, ndev);
+
+    gdy_ctx *ctx = new gdy_ctx();
+    ctx->device = device; ctx->rank = rank; ctx->world = world;
+    ctx->n = n; ctx->npad = round_up(n, PAD);
+    ctx->e2 = e2; ctx->eta = eta; ctx->mask_self = (e2 == 0.0);
+    c = ctx;
+    int rc = 0;
+    do {
+        if ((rc = bind_device(c))) break;
+        cudaDeviceProp prop;
+        if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) { rc = fail(c, GDY_ERR_CUDA, "cudaGetDeviceProperties failed"); break; }
+        if (prop.major < 10) { rc = fail(c, GDY_ERR_NO_DEVICE, "device %d is sm_%d%d; this library is built for sm_100a only", device, prop.major, prop.minor); break; }
+        c->num_sms = prop.multiProcessorCount;
+        auto cu = [&](cudaError_t e, const char *what) { if (e != cudaSuccess && !rc) rc = fail(c, GDY_ERR_CUDA, "%s: %s", what, cudaGetErrorString(e)); };
+        cu(cudaStreamCreateWithFlags(&c->st, cudaStreamNonBlocking), "cudaStreamCreate");
+        cu(cudaEventCreate(&c->ev0), "cudaEventCreate");
+        cu(cudaEventCreate(&c->ev1), "cudaEventCreate");
+        if (rc) break;
+        if ((rc = alloc_all(c))) break;
+        // contiguous, tile-aligned j-shards (reference partition: src/include/gpu/Hermite4GPU.cu:81-97)
+        const uint32_t ntile = c->npad / TJ;
+        c->tile_begin = (uint32_t)((uint64_t)ntile * rank / world);
+        c->tile_end = (uint32_t)((uint64_t)ntile * (rank + 1) / world);
+        if (world > 1)
+        {
+            if (!nccl_load()) { rc = fail(c, GDY_ERR_NCCL, "libnccl.so.2 not loadable: %s", dlerror()); break; }
+            ncclUniqueId id;
+            memcpy(&id, nccl_uid, sizeof id);
+            ncclResult_t r = g_nccl.CommInitRank(&c->comm, world, id, rank);
+            if (r != ncclSuccess) { rc = fail(c, GDY_ERR_NCCL, "ncclCommInitRank: %s", g_nccl.GetErrorString(r)); break; }
+        }
+    } while (0);
+    if (rc)
+    {
+        snprintf(g_create_err, sizeof g_create_err, "%s", c->err);
+        gdy_destroy(c);
+        return rc;
+    }
+    *out = c;
+    return GDY_OK;
+}
+
+extern "C" int gdy_create(gdy_ctx **out, uint32_t n, double e2, float eta, int device)
+{
+    return gdy_create_sharded(out, n, e2, eta, device, 0, 1, nullptr);
+}
+
+extern "C" int gdy_destroy(gdy_ctx *c)
+{
+    if (!c) return GDY_OK;
+    cudaSetDevice(c->device);
+    if (c->st) cudaStreamSynchronize(c->st);
+    if (c->comm && g_nccl.ok) g_nccl.CommDestroy(c->comm);
+    cudaFree(c->pool); cudaFree(c->d_move); cudaFree(c->d_ilist); cudaFree(c->d_block_cnt);
+    cudaFree(c->d_block_min); cudaFree(c->d_sched); cudaFree(c->d_atime); cudaFree(c->d_energy);
+    cudaFree(c->d_stage);
+    if (c->pin) cudaFreeHost(c->pin);
+    if (c->ev0) cudaEventDestroy(c->ev0);
+    if (c->ev1) cudaEventDestroy(c->ev1);
+    if (c->st) cudaStreamDestroy(c->st);
+    delete c;
+    return GDY_OK;
+}
+
+// ---- state transfer ------------------------------------------------------------------------------------
+namespace {
+
+// host AoS (n x stride doubles) -> device columns.  cols[k] == NULL skips AoS column k.
+int upload_cols(gdy_ctx *c, const double *host, int stride, int ncol, double *const *cols)
+{
+    Cols cc{};
+    for (int k = 0; k < ncol; ++k) cc.c[k] = cols[k];
+    CU(cudaMemcpyAsync(c->d_stage, host, (size_t)c->n * stride * sizeof(double), cudaMemcpyHostToDevice, c->st));
+    k_unpack<<<cdiv(c->n, 256), 256, 0, c->st>>>(c->d_stage, cc, ncol, stride, c->n);
+    LAUNCHED(c);
+    CU(cudaStreamSynchronize(c->st));   // host buffer is borrowed for the call only
+    return 0;
+}
+
+int download_cols(gdy_ctx *c, double *host, int stride, int ncol, double *const *cols)
+{
+    Cols cc{};
+    for (int k = 0; k < ncol; ++k) cc.c[k] = cols[k];
+    k_pack<<<cdiv(c->n, 256), 256, 0, c->st>>>(c->d_stage, cc, ncol, stride, c->n);
+    LAUNCHED(c);
+    CU(cudaMemcpyAsync(host, c->d_stage, (size_t)c->n * stride * sizeof(double), cudaMemcpyDeviceToHost, c->st));
+    CU(cudaStreamSynchronize(c->st));
+    return 0;
+}
+
+}  // namespace
+
+extern "C" int gdy_upload_particles(gdy_ctx *c, const double *r4, const double *v4)
+{
+    if (!c) return GDY_ERR_INVALID;
+    if (!r4 || !v4) return fail(c, GDY_ERR_INVALID, "r4/v4 is NULL");
+    BIND(c);
+    State &s = c->s;
+    double *rc[4] = {s.x, s.y, s.z, s.m};
+    double *vc[4] = {s.vx, s.vy, s.vz, nullptr};
+    int r;
+    if ((r = upload_cols(c, r4, 4, 4, rc))) return r;
+    if ((r = upload_cols(c, v4, 4, 4, vc))) return r;
+    c->have_particles = true;
+    c->have_pred = false;
+    return GDY_OK;
+}
+
+extern "C" int gdy_upload_times(gdy_ctx *c, const double *t, const double *dt)
+{
+    if (!c) return GDY_ERR_INVALID;
+    if (!t || !dt) return fail(c, GDY_ERR_INVALID, "t/dt is NULL");
+    BIND(c);
+    CU(cudaMemcpyAsync(c->s.t, t, (size_t)c->n * sizeof(double), cudaMemcpyHostToDevice, c->st));
+    CU(cudaMemcpyAsync(c->s.dt, dt, (size_t)c->n * sizeof(double), cudaMemcpyHostToDevice, c->st));
+    CU(cudaStreamSynchronize(c->st));
+    return GDY_OK;
+}
+
+extern "C" int gdy_upload_forces(gdy_ctx *c, const double *f6)
+{
+    if (!c) return GDY_ERR_INVALID;
+    if (!f6) return fail(c, GDY_ERR_INVALID, "f6 is NULL");
+    BIND(c);
+    return upload_cols(c, f6, 6, 6, c->s.f);
+}
+
+extern "C" int gdy_upload_derivs(gdy_ctx *c, const double *old6, const double *a2, const double *a3)
+{
+    if (!c) return GDY_ERR_INVALID;
+    BIND(c);
+    int r;
+    if (old6 && (r = upload_cols(c, old6, 6, 6, c->s.old))) return r;
+    if (a2 && (r = upload_cols(c, a2, 3, 3, c->s.a2))) return r;
+    if (a3 && (r = upload_cols(c, a3, 3, 3, c->s.a3))) return r;
+    return GDY_OK;
+}
+
+extern "C" int gdy_download_forces(gdy_ctx *c, double *f6)
+{
+    if (!c) return GDY_ERR_INVALID;
+    if (!f6) return fail(c, GDY_ERR_INVALID, "f6 is NULL");
+    BIND(c);
+    return download_cols(c, f6, 6, 6, c->s.f);
+}
+
+extern "C" int gdy_download_state(gdy_ctx *c, double *r4, double *v4, double *f6, double *old6, double *a2,
+                                  double *a3, double *t, double *dt, double *p7, uint32_t *move)
+{
+    if (!c) return GDY_ERR_INVALID;
+    BIND(c);
+    State &s = c->s;
+    int r;
+    double *rc[4] = {s.x, s.y, s.z, s.m};
+    double *vc[4] = {s.vx, s.vy, s.vz, nullptr};
+    double *pc[7] = {s.p[0], s.p[1], s.p[2], s.p[3], s.p[4], s.p[5], s.m};
+    if (r4 && (r = download_cols(c, r4, 4, 4, rc))) return r;
+    if (v4 && (r = download_cols(c, v4, 4, 4, vc))) return r;
+    if (f6 && (r = download_cols(c, f6, 6, 6, s.f))) return r;
+    if (old6 && (r = download_cols(c, old6, 6, 6, s.old))) return r;
+    if (a2 && (r = download_cols(c, a2, 3, 3, s.a2))) return r;
+    if (a3 && (r = download_cols(c, a3, 3, 3, s.a3))) return r;
+    if (p7 && (r = download_cols(c, p7, 7, 7, pc))) return r;
+    if (t) CU(cudaMemcpyAsync(t, s.t, (size_t)c->n * sizeof(double), cudaMemcpyDeviceToHost, c->st));
+    if (dt) CU(cudaMemcpyAsync(dt, s.dt, (size_t)c->n * sizeof(double), cudaMemcpyDeviceToHost, c->st));
+    if (move) CU(cudaMemcpyAsync(move, s.move, (size_t)c->n * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->st));
+    CU(cudaStreamSynchronize(c->st));
+    if (move)   // entries past the active count read -1, as the reference leaves them (Hermite4.cpp:69)
+        for (uint32_t k = c->last_nact; k < c->n; ++k) move[k] = 0xFFFFFFFFu;
+    return GDY_OK;
+}
+
+// ---- the force path --------------------------------------------------------------------------------------
+namespace {
+
+struct ForcePlan
+{
+    int variant;
+    dim3 grid;
+    uint32_t jb, je, per_split, nsplit, ld;
+};
+
+// Which kernel for how many active particles.  Large blocks: i in registers, j through the TMA ring,
+// biggest i-tile that still leaves every SM busy.  Small blocks: j across lanes (k_force_lane).  The
+// j-split is chosen so that (i-tiles x j-splits) covers the machine a few times over.
+int pick_variant(const gdy_ctx *c, uint32_t nact)
+{
+    if (c->tune_variant >= 0 && c->tune_variant < FV_COUNT) return c->tune_variant;
+    if (nact <= 1) return FV_LANE_I1;
+    if (nact <= 2) return FV_LANE_I2;
+    if (nact <= 4) return FV_LANE_I4;
+    if (nact <= 8) return FV_LANE_I8;
+    if (nact <= 16) return FV_LANE_I16;
+    if (nact <= 32) return FV_TILE_I32;
+    if (nact <= 64) return FV_TILE_I64;
+    const uint32_t full = (uint32_t)c->num_sms * 4;   // CTAs of 128 threads that fill the machine
+    if (nact >= 256 * full) return FV_TILE_I256;
+    if (nact % 256 > 0 && nact % 256 <= 128 && nact < 4096) return FV_TILE_I128;
+    return nact >= 1024 ? FV_TILE_I256 : FV_TILE_I128;
+}
+
+ForcePlan plan_force(const gdy_ctx *c, uint32_t nact)
+{
+    ForcePlan p{};
+    p.variant = pick_variant(c, nact);
+    const ForceVariant &v = g_variants[p.variant];
+    const uint32_t gx = cdiv(nact, (uint32_t)v.ti);
+    const uint32_t target = (uint32_t)c->num_sms * (v.threads >= 256 ? 3u : 6u);
+    p.ld = round_up(nact, 32);
+    uint32_t units;   // j work items that can be split: tiles (tile kernels) or trips (lane kernels)
+    if (v.kind == 0)
+    {
+        p.jb = c->tile_begin; p.je = c->tile_end;
+        units = p.je - p.jb;
+    }
+    else
+    {
+        p.jb = c->tile_begin * TJ;
+        p.je = c->tile_end * TJ < c->n ? c->tile_end * TJ : c->n;
+        if (p.je < p.jb) p.je = p.jb;
+        units = cdiv(p.je - p.jb, (uint32_t)v.pj);
+    }
+    uint32_t split = gx >= target ? 1u : cdiv(target, gx);
+    if (c->tune_jsplit > 0) split = (uint32_t)c->tune_jsplit;
+    const size_t max_split = c->part_cap / ((size_t)6 * p.ld);
+    if (split > max_split) split = (uint32_t)max_split;
+    if (split > units) split = units;
+    if (split < 1) split = 1;
+    uint32_t per = units ? cdiv(units, split) : 1;
+    split = units ? cdiv(units, per) : 1;
+    p.nsplit = split;
+    p.per_split = v.kind == 0 ? per : per * (uint32_t)v.pj;
+    p.grid = dim3(gx, split, 1);
+    return p;
+}
+
+// Partial forces of `nact` i-particles (k-indexed views iv) against this shard's j-particles, summed
+// over the j-splits and over the shards.  *out = k-indexed [6][ld] buffer holding the result.
+int force_eval(gdy_ctx *c, uint32_t nact, IView iv, const double **out, uint32_t *ld_out, bool timed)
+{
+    const State &s = c->s;
+    const ForcePlan p = plan_force(c, nact);
+    JView jv{s.p[0], s.p[1], s.p[2], s.p[3], s.p[4], s.p[5], s.m};
+    if (timed) CU(cudaEventRecord(c->ev0, c->st));
+    cudaError_t e = c->mask_self
+        ? launch_force<true>(p.variant, p.grid, c->st, jv, iv, s.part, nact, p.ld, p.jb, p.je, p.per_split, c->e2)
+        : launch_force<false>(p.variant, p.grid, c->st, jv, iv, s.part, nact, p.ld, p.jb, p.je, p.per_split, c->e2);
+    ++c->launches;
+    if (e != cudaSuccess) return fail(c, GDY_ERR_CUDA, "force kernel %s grid (%u,%u): %s", g_variants[p.variant].name, p.grid.x, p.grid.y, cudaGetErrorString(e));
+    double *buf = s.part;
+    if (p.nsplit > 1)
+    {
+        k_reduce_partials<<<cdiv(nact, 32), 256, 0, c->st>>>(s.part, s.fsum, nact, p.ld, p.nsplit);
+        LAUNCHED(c);
+        buf = s.fsum;
+    }
+    if (timed) CU(cudaEventRecord(c->ev1, c->st));
+    if (c->world > 1)
+        NC(g_nccl.AllReduce(buf, buf, (size_t)6 * p.ld, ncclDouble, ncclSum, c->comm, c->st));
+    *out = buf;
+    *ld_out = p.ld;
+    return 0;
+}
+
+IView active_view(const State &s) { return IView{s.ip[0], s.ip[1], s.ip[2], s.ip[3], s.ip[4], s.ip[5]}; }
+IView identity_view(const State &s) { return IView{s.p[0], s.p[1], s.p[2], s.p[3], s.p[4], s.p[5]}; }
+
+int need_particles(gdy_ctx *c)
+{
+    if (!c->have_particles) return fail(c, GDY_ERR_STATE, "no particles uploaded (gdy_upload_particles)");
+    return 0;
+}
+
+}  // namespace
+
+extern "C" int gdy_set_tuning(gdy_ctx *c, int variant, int jsplit)
+{
+    if (!c) return GDY_ERR_INVALID;
+    if (variant >= FV_COUNT) return fail(c, GDY_ERR_INVALID, "variant %d out of range (< %d)", variant, (int)FV_COUNT);
+    c->tune_variant = variant;
+    c->tune_jsplit = jsplit;
+    return GDY_OK;
+}
+
+extern "C" int gdy_init_acc_jrk(gdy_ctx *c)
+{
+    if (!c) return GDY_ERR_INVALID;
+    BIND(c);
+    int r;
+    if ((r = need_particles(c))) return r;
+    State &s = c->s;
+    k_copy_to_pred<<<cdiv(c->n, 256), 256, 0, c->st>>>(s, c->n);
+    LAUNCHED(c);
+    c->have_pred = true;
+    const double *buf; uint32_t ld;
+    if ((r = force_eval(c, c->n, identity_view(s), &buf, &ld, false))) return r;
+    k_scatter_forces<<<cdiv(c->n, 256), 256, 0, c->st>>>(s, nullptr, c->n, buf, ld);
+    LAUNCHED(c);
+    return GDY_OK;
+}
+
+extern "C" int gdy_init_dt(gdy_ctx *c, float eta_s, double itime, double *atime_out)
+{
+    if (!c) return GDY_ERR_INVALID;
+    BIND(c);
+    // Host arithmetic with libm log/pow/ceil exactly as the reference does it (src/include/Hermite4.cpp:
+    // 108-140): a device log could round differently and flip a timestep level.
+    std::vector<double> f((size_t)c->n * 6), t(c->n), dt(c->n);
+    int r;
+    if ((r = gdy_download_forces(c, f.data()))) return r;
+    double ctime = 1.0e+10;   // reference: Hermite4CPU_integration.cpp:43
+    for (uint32_t i = 0; i < c->n; ++i)
+    {
+        const double *fi = &f[(size_t)i * 6];
+        const double amag = std::sqrt(fi[0] * fi[0] + fi[1] * fi[1] + fi[2] * fi[2]);
+        const double jmag = std::sqrt(fi[3] * fi[3] + fi[4] * fi[4] + fi[5] * fi[5]);
+        double step = eta_s * (amag / jmag);
+        const int level = (int)(std::ceil(std::log(step) / std::log(2.0)) - 1);
+        step = std::pow(2, level);
+        if (step < D_TIME_MIN) step = D_TIME_MIN;
+        else if (step > D_TIME_MAX) step = D_TIME_MAX;
+        dt[i] = step;
+        t[i] = itime;
+        if (step < ctime) ctime = step;
+    }
+    if ((r = gdy_upload_times(c, t.data(), dt.data()))) return r;
+    if (atime_out) *atime_out = ctime;
+    return GDY_OK;
+}
+
+// ---- the per-step hooks ------------------------------------------------------------------------------------
+namespace {
+
+// find_particles_to_move on the device.  from_min: ITIME = the minimum left in d_block_min by
+// k_min_time (chained scheduler), else the `itime` argument.  Leaves {itime, nact} in the pinned slot.
+int launch_sched(gdy_ctx *c, double itime, bool from_min)
+{
+    State &s = c->s;
+    const double *bm = from_min ? c->d_block_min : nullptr;
+    ++c->seq;
+    k_sched_count<<<c->n_sched_blocks, SCHED_BLOCK, 0, c->st>>>(s, c->n, itime, bm, c->n_min_blocks, c->d_block_cnt);
+    LAUNCHED(c);
+    k_sched_write<<<c->n_sched_blocks, SCHED_BLOCK, 0, c->st>>>(s, c->n, itime, bm, c->n_min_blocks, c->d_block_cnt,
+                                                               c->n_sched_blocks, c->d_sched, &c->pin->sched, c->seq);
+    LAUNCHED(c);
+    return 0;
+}
+
+int launch_min_time(gdy_ctx *c)
+{
+    k_min_time<<<c->n_min_blocks, 256, 0, c->st>>>(c->s, c->n, c->d_block_min);
+    LAUNCHED(c);
+    return 0;
+}
+
+// predicted_pos_vel for this shard's j-slice (world == 1: everybody)
+int launch_predict(gdy_ctx *c, double itime)
+{
+    uint32_t b = c->tile_begin * TJ, e = c->tile_end * TJ;
+    if (e > c->n) e = c->n;
+    if (e > b)
+    {
+        k_predict<<<cdiv(e - b, 256), 256, 0, c->st>>>(c->s, b, e, itime);
+        LAUNCHED(c);
+    }
+    c->have_pred = true;
+    return 0;
+}
+
+}  // namespace
+
+extern "C" int gdy_find_particles_to_move(gdy_ctx *c, double itime, uint32_t *nact_out)
+{
+    if (!c) return GDY_ERR_INVALID;
+    BIND(c);
+    int r;
+    if ((r = launch_sched(c, itime, false))) return r;
+    CU(cudaStreamSynchronize(c->st));
+    c->last_nact = c->pin->sched.nact;
+    if (nact_out) *nact_out = c->last_nact;
+    return GDY_OK;
+}
+
+extern "C" int gdy_save_old_acc_jrk(gdy_ctx *c, uint32_t nact)
+{
+    if (!c) return GDY_ERR_INVALID;
+    if (nact > c->n) return fail(c, GDY_ERR_INVALID, "nact %u > n %u", nact, c->n);
+    BIND(c);
+    if (nact == 0) return GDY_OK;
+    k_save_old<<<cdiv(nact, 128), 128, 0, c->st>>>(c->s, nact);
+    LAUNCHED(c);
+    return GDY_OK;
+}
+
+extern "C" int gdy_predicted_pos_vel(gdy_ctx *c, double itime)
+{
+    if (!c) return GDY_ERR_INVALID;
+    BIND(c);
+    int r;
+    if ((r = need_particles(c))) return r;
+    if (c->world == 1) return launch_predict(c, itime);
+    // hook semantics = all N particles predicted on every shard (the fused driver predicts only the
+    // shard's slice plus the active particles)
+    k_predict<<<cdiv(c->n, 256), 256, 0, c->st>>>(c->s, 0, c->n, itime);
+    LAUNCHED(c);
+    c->have_pred = true;
+    return GDY_OK;
+}
+
+extern "C" int gdy_update_acc_jrk(gdy_ctx *c, uint32_t nact)
+{
+    if (!c) return GDY_ERR_INVALID;
+    if (nact > c->n) return fail(c, GDY_ERR_INVALID, "nact %u > n %u", nact, c->n);
+    BIND(c);
+    if (!c->have_pred) return fail(c, GDY_ERR_STATE, "update_acc_jrk before predicted_pos_vel/init_acc_jrk");
+    if (nact == 0) return GDY_OK;
+    State &s = c->s;
+    k_gather_active<<<cdiv(nact, 128), 128, 0, c->st>>>(s, s.move, nact, 0, 0, 0.0);
+    LAUNCHED(c);
+    const double *buf; uint32_t ld;
+    int r;
+    if ((r = force_eval(c, nact, active_view(s), &buf, &ld, false))) return r;
+    k_scatter_forces<<<cdiv(nact, 128), 128, 0, c->st>>>(s, s.move, nact, buf, ld);
+    LAUNCHED(c);
+    return GDY_OK;
+}
+
+extern "C" int gdy_correction_pos_vel(gdy_ctx *c, double itime, uint32_t nact)
+{
+    if (!c) return GDY_ERR_INVALID;
+    if (nact > c->n) return fail(c, GDY_ERR_INVALID, "nact %u > n %u", nact, c->n);
+    BIND(c);
+    if (nact == 0) return GDY_OK;
+    k_correct<<<cdiv(nact, 128), 128, 0, c->st>>>(c->s, nact, itime, (double)c->eta, nullptr, 0);
+    LAUNCHED(c);
+    return GDY_OK;
+}
+
+extern "C" int gdy_next_integration_time(gdy_ctx *c, double *atime_out)
+{
+    if (!c) return GDY_ERR_INVALID;
+    BIND(c);
+    int r;
+    if ((r = launch_min_time(c))) return r;
+    k_min_final<<<1, 256, 0, c->st>>>(c->d_block_min, c->n_min_blocks, c->d_atime, &c->pin->atime);
+    LAUNCHED(c);
+    CU(cudaStreamSynchronize(c->st));
+    if (atime_out) *atime_out = c->pin->atime;
+    return GDY_OK;
+}
+
+extern "C" int gdy_energy(gdy_ctx *c, double *ekin_out, double *epot_out)
+{
+    if (!c) return GDY_ERR_INVALID;
+    BIND(c);
+    int r;
+    if ((r = need_particles(c))) return r;
+    State &s = c->s;
+    // per-particle terms go to the (idle between steps) partial-force scratch
+    double *ek = s.part, *ep = s.part + c->npad;
+    k_energy<<<cdiv(c->n, 128), 128, 0, c->st>>>(s, c->n, c->npad, ek, ep);
+    LAUNCHED(c);
+    k_sum2<<<1, 1024, 0, c->st>>>(ek, ep, c->n, c->d_energy);
+    LAUNCHED(c);
+    CU(cudaMemcpyAsync(c->pin->energy, c->d_energy, 2 * sizeof(double), cudaMemcpyDeviceToHost, c->st));
+    CU(cudaStreamSynchronize(c->st));
+    if (ekin_out) *ekin_out = c->pin->energy[0];
+    if (epot_out) *epot_out = c->pin->energy[1];
+    return GDY_OK;
+}
+
+extern "C" uint64_t gdy_launch_count(const gdy_ctx *c) { return c ? c->launches : 0; }
+
+extern "C" int gdy_sync(gdy_ctx *c)
+{
+    if (!c) return GDY_ERR_INVALID;
+    BIND(c);
+    CU(cudaStreamSynchronize(c->st));
+    return GDY_OK;
+}
+
+// ---- fused driver ----------------------------------------------------------------------------------------
+// The reference loop body (src/include/cpu/Hermite4CPU_integration.cpp:81-124) with everything on the
+// device and ONE host readback per block step ({next block time, next nact}, 16 bytes of pinned
+// memory): the scheduler of step k+1 is chained behind the corrector of step k.
+extern "C" int gdy_run(gdy_ctx *c, double atime, double itime0, double t_stop, uint64_t max_steps,
+                       gdy_run_stats *stats, uint32_t *trace_nact, double *trace_itime, uint64_t trace_cap)
+{
+    if (!c) return GDY_ERR_INVALID;
+    BIND(c);
+    int r;
+    if ((r = need_particles(c))) return r;
+    State &s = c->s;
+    const auto w0 = std::chrono::steady_clock::now();
+    const bool timed = c->tune_variant == -2 ? false : (stats != nullptr && getenv("GDY_TIME_FORCE") != nullptr);
+    uint64_t it = 0, nsteps = 0, inter = 0;
+    double force_ms = 0.0;
+    double ITIME = itime0, ATIME = atime;
+
+    if (ITIME < t_stop && !(max_steps && it >= max_steps))
+    {
+        if ((r = launch_sched(c, ATIME, false))) return r;
+        CU(cudaStreamSynchronize(c->st));
+    }
+    while (ITIME < t_stop)
+    {
+        if (max_steps && it >= max_steps) break;
+        ITIME = ATIME;
+        const uint32_t nact = c->pin->sched.nact;
+        c->last_nact = nact;
+        const bool last = !(ITIME < t_stop) || (max_steps && it + 1 >= max_steps);
+        if (nact == 0) return fail(c, GDY_ERR_STATE, "no particle is due at block time %.17g", ITIME);
+
+        if ((r = launch_predict(c, ITIME))) return r;
+        k_gather_active<<<cdiv(nact, 128), 128, 0, c->st>>>(s, s.move, nact, 1, c->world > 1 ? 1 : 0, ITIME);
+        LAUNCHED(c);
+        const double *buf; uint32_t ld;
+        if ((r = force_eval(c, nact, active_view(s), &buf, &ld, timed))) return r;
+        k_correct<<<cdiv(nact, 128), 128, 0, c->st>>>(s, nact, ITIME, (double)c->eta, buf, ld);
+        LAUNCHED(c);
+        if ((r = launch_min_time(c))) return r;
+        if (last)
+        {
+            k_min_final<<<1, 256, 0, c->st>>>(c->d_block_min, c->n_min_blocks, c->d_atime, &c->pin->atime);
+            LAUNCHED(c);
+        }
+        else if ((r = launch_sched(c, 0.0, true))) return r;
+        CU(cudaStreamSynchronize(c->st));
+        ATIME = last ? c->pin->atime : c->pin->sched.itime;
+        if (timed)
+        {
+            float ms = 0.f;
+            CU(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+            force_ms += ms;
+        }
+        if (it < trace_cap)
+        {
+            if (trace_nact) trace_nact[it] = nact;
+            if (trace_itime) trace_itime[it] = ITIME;
+        }
+        inter += (uint64_t)nact * (uint64_t)c->n;
+        nsteps += nact;
+        ++it;
+    }
+    if (stats)
+    {
+        stats->iterations = it; stats->nsteps = nsteps; stats->interactions = inter;
+        stats->itime = ITIME; stats->atime = ATIME; stats->force_ms = force_ms;
+        stats->wall_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - w0).count();
+    }
+    return GDY_OK;
+}
+
+// ---- bench / test entry points -----------------------------------------------------------------------------
+extern "C" int gdy_force_sweep(gdy_ctx *c, uint32_t nact, const uint32_t *move, double *f6_out, float *ms_out)
+{
+    if (!c) return GDY_ERR_INVALID;
+    if (nact == 0 || nact > c->n || !move) return fail(c, GDY_ERR_INVALID, "bad active list (nact %u, n %u)", nact, c->n);
+    BIND(c);
+    if (!c->have_pred) return fail(c, GDY_ERR_STATE, "force_sweep before predicted_pos_vel/init_acc_jrk");
+    for (uint32_t k = 0; k < nact; ++k)
+        if (move[k] >= c->n) return fail(c, GDY_ERR_INVALID, "move[%u] = %u out of range", k, move[k]);
+    State &s = c->s;
+    CU(cudaMemcpyAsync(c->d_ilist, move, (size_t)nact * sizeof(uint32_t), cudaMemcpyHostToDevice, c->st));
+    k_gather_active<<<cdiv(nact, 128), 128, 0, c->st>>>(s, c->d_ilist, nact, 0, 0, 0.0);
+    LAUNCHED(c);
+    const double *buf; uint32_t ld;
+    int r;
+    if ((r = force_eval(c, nact, active_view(s), &buf, &ld, true))) return r;
+    if (f6_out)
+    {
+        std::vector<double> tmp((size_t)6 * ld);
+        CU(cudaMemcpyAsync(tmp.data(), buf, tmp.size() * sizeof(double), cudaMemcpyDeviceToHost, c->st));
+        CU(cudaStreamSynchronize(c->st));
+        for (uint32_t k = 0; k < nact; ++k)
+            for (int q = 0; q < 6; ++q) f6_out[(size_t)k * 6 + q] = tmp[(size_t)q * ld + k];
+    }
+    else CU(cudaStreamSynchronize(c->st));
+    if (ms_out) CU(cudaEventElapsedTime(ms_out, c->ev0, c->ev1));
+    return GDY_OK;
+}
+
+extern "C" int gdy_force_sweep_full(gdy_ctx *c, int reps, float *ms_out)
+{
+    if (!c) return GDY_ERR_INVALID;
+    if (reps < 1) return fail(c, GDY_ERR_INVALID, "reps must be >= 1");
+    BIND(c);
+    if (!c->have_pred) return fail(c, GDY_ERR_STATE, "force_sweep_full before predicted_pos_vel/init_acc_jrk");
+    cudaEvent_t a, b;
+    CU(cudaEventCreate(&a)); CU(cudaEventCreate(&b));
+    CU(cudaEventRecord(a, c->st));
+    const double *buf; uint32_t ld;
+    for (int i = 0; i < reps; ++i)
+    {
+        int r = force_eval(c, c->n, identity_view(c->s), &buf, &ld, false);
+        if (r) return r;
+    }
+    CU(cudaEventRecord(b, c->st));
+    CU(cudaStreamSynchronize(c->st));
+    float ms = 0.f;
+    CU(cudaEventElapsedTime(&ms, a, b));
+    cudaEventDestroy(a); cudaEventDestroy(b);
+    if (ms_out) *ms_out = ms / reps;
+    return GDY_OK;
+}
+
+// ---- roofline denominators (measurement infrastructure) ------------------------------------------------------
+extern "C" int gdy_measure_fp64_peak(gdy_ctx *c, double *tflops_out, double *sm_mhz_out)
+{
+    if (!c) return GDY_ERR_INVALID;
+    BIND(c);
+    const int blocks = c->num_sms * 4, iters = 4096;   // one resident wave: 1024 threads per SM
+    double *out = c->s.part;                           // scratch
+    long long *cyc;
+    CU(cudaMalloc(&cyc, sizeof(long long)));
+    float best = 1e30f;
+    long long cycles = 0;
+    for (int rep = 0; rep < 6; ++rep)
+    {
+        CU(cudaEventRecord(c->ev0, c->st));
+        k_dfma_peak<<<blocks, 256, 0, c->st>>>(out, iters, 1.0000001, 1e-9, cyc);
+        LAUNCHED(c);
+        CU(cudaEventRecord(c->ev1, c->st));
+        CU(cudaStreamSynchronize(c->st));
+        float ms;
+        CU(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+        if (rep >= 2 && ms < best)
+        {
+            best = ms;
+            CU(cudaMemcpy(&cycles, cyc, sizeof cycles, cudaMemcpyDeviceToHost));
+        }
+    }
+    cudaFree(cyc);
+    const double flop = 2.0 * 64.0 * iters * 256.0 * blocks;
+    if (tflops_out) *tflops_out = flop / (best * 1e-3) / 1e12;
+    if (sm_mhz_out) *sm_mhz_out = (double)cycles / (best * 1e-3) / 1e6;
+    return GDY_OK;
+}
+
+extern "C" int gdy_measure_copy_bw(gdy_ctx *c, double *gbs_out)
+{
+    if (!c) return GDY_ERR_INVALID;
+    BIND(c);
+    const size_t bytes = (size_t)1 << 30;
+    char *a, *b;
+    CU(cudaMalloc(&a, bytes)); CU(cudaMalloc(&b, bytes));
+    CU(cudaMemsetAsync(a, 1, bytes, c->st));
+    float best = 1e30f;
+    for (int rep = 0; rep < 6; ++rep)
+    {
+        CU(cudaEventRecord(c->ev0, c->st));
+        CU(cudaMemcpyAsync(b, a, bytes, cudaMemcpyDeviceToDevice, c->st));
+        CU(cudaEventRecord(c->ev1, c->st));
+        CU(cudaStreamSynchronize(c->st));
+        float ms;
+        CU(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+        if (rep >= 1 && ms < best) best = ms;
+    }
+    cudaFree(a); cudaFree(b);
+    if (gbs_out) *gbs_out = 2.0 * bytes / (best * 1e-3) / 1e9;
+    return GDY_OK;
+}

@@ -1,0 +1,143 @@
+// gdy_device.cuh — device-side building blocks shared by every kernel of the Hermite4 hot path.
+// sm_100a only.  No reference code is reproduced here; reference citations say what each piece
+// replaces or must agree with.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace gdy {
+
+// j-tile size staged per pipeline stage, and the padding granule of every particle array.
+constexpr int TJ = 128;          // particles per TMA-staged j-tile (7 arrays x 1 KiB per stage)
+constexpr int NSTAGE = 4;        // pipeline depth of the j-tile ring
+constexpr int PAD = 256;         // arrays are padded to a multiple of this (zero-mass far particles)
+constexpr double PAD_POS = 1.0e10;  // where the padding particles sit (mass 0 => contribute exactly 0)
+
+// Device-resident particle state, structure-of-arrays, every array npad doubles.
+// Reference data contract: double4 h_r{x,y,z,m}, double4 h_v, Forces h_f/h_old, double3 h_a2/h_a3,
+// double h_t/h_dt, Predictor h_p (reference: src/include/NbodySystem.hpp:100-115,
+// src/include/common.hpp:213-231).  Mass is a float-representable double (Predictor.m is float).
+struct State
+{
+    double *x, *y, *z, *m;          // h_r
+    double *vx, *vy, *vz;           // h_v
+    double *f[6];                   // h_f   : ax ay az jx jy jz
+    double *old[6];                 // h_old
+    double *a2[3], *a3[3];          // h_a2, h_a3
+    double *t, *dt;                 // h_t, h_dt
+    double *p[6];                   // h_p   : predicted x y z vx vy vz (mass shared with m)
+    uint32_t *move;                 // h_move
+    double *ip[6];                  // predicted pos/vel of the active list, gathered (k-indexed)
+    double *fsum;                   // [6][nact_pad] summed partial forces of the active list
+    double *part;                   // [S][6][nact_pad] j-split partial forces
+};
+
+struct JView { const double *x, *y, *z, *vx, *vy, *vz, *m; };
+struct IView { const double *x, *y, *z, *vx, *vy, *vz; };
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p)
+{
+    return (uint32_t)__cvta_generic_to_shared(p);
+}
+
+// ---- mbarrier + 1-D TMA bulk copy (cp.async.bulk, SASS UBLKCP) -----------------------------------
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_fence_init()
+{
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)),
+                 "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t *bar, uint32_t parity)
+{
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
+{
+    while (!mbar_try_wait(bar, parity)) { }
+}
+// global -> shared bulk copy, completion counted in bytes on `bar`.  bytes % 16 == 0, both
+// addresses 16-byte aligned.
+__device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src_gmem, uint32_t bytes,
+                                         uint64_t *bar)
+{
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::
+            "r"(smem_u32(dst_smem)),
+        "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+        : "memory");
+}
+
+// ---- FP64 reciprocal square root -------------------------------------------------------------
+// Seed: rsqrt.approx.ftz.f64 (SASS MUFU.RSQ64H: the SFU's FP32-precision table applied to the high
+// word, ~2^-22 relative error, runs on the XU pipe, not the FP64 pipe).  One cubically convergent
+// correction y1 = y0 + y0*e*(1/2 + 3e/8), e = 1 - a*y0^2, leaves 5e^3/16 ~ 2^-64 of truncation error:
+// full double precision for 5 FP64-pipe instructions.  Replaces rsqrt() in k_force_calculation
+// (reference: src/include/gpu/Hermite4GPU_kernels.cu:101) / 1.0/sqrt() in the CPU oracle
+// (reference: src/include/cpu/Hermite4CPU.cpp:66).
+__device__ __forceinline__ double rsqrt_seed(double a)
+{
+    double y;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(a));
+    return y;
+}
+__device__ __forceinline__ double rsqrt_f64(double a)
+{
+    const double y0 = rsqrt_seed(a);
+    const double t = a * y0;
+    const double e = fma(-t, y0, 1.0);
+    const double p = fma(0.375, e, 0.5);
+    const double q = y0 * e;
+    return fma(p, q, y0);
+}
+
+// ---- the pair interaction -----------------------------------------------------------------------
+// acc += m r / |r|^3 ; jerk += m ( v/|r|^3 - 3 (r.v) r / |r|^5 ), |r|^2 softened by e2.
+// Same quantities as Hermite4CPU::force_calculation (reference: src/include/cpu/Hermite4CPU.cpp:55-82)
+// arranged for the FP64 pipe: 6 DADD + 3 DFMA (r2) + DMUL,2 DFMA (r.v) + 5 (rsqrt) + 3 DMUL + 2 DMUL +
+// 3 DFMA (acc) + 6 DFMA (jerk) = 31 FP64-pipe instructions per pair, FMA-contracted (tolerance of
+// the north star for acc/jerk is 1e-12 relative; contraction and summation order are within it).
+struct Acc6 { double ax, ay, az, jx, jy, jz; };
+
+template <bool MASK_SELF>
+__device__ __forceinline__ void pair(Acc6 &s, double xi, double yi, double zi, double vxi,
+                                     double vyi, double vzi, double xj, double yj, double zj,
+                                     double vxj, double vyj, double vzj, double mj, double e2)
+{
+    const double dx = xj - xi, dy = yj - yi, dz = zj - zi;
+    const double dvx = vxj - vxi, dvy = vyj - vyi, dvz = vzj - vzi;
+    double r2 = fma(dx, dx, e2);
+    r2 = fma(dy, dy, r2);
+    r2 = fma(dz, dz, r2);
+    double rv = dx * dvx;
+    rv = fma(dy, dvy, rv);
+    rv = fma(dz, dvz, rv);
+    double y = rsqrt_f64(r2);
+    if (MASK_SELF) y = (r2 > 0.0) ? y : 0.0;   // e2 == 0: drop the i == j self pair (CPU oracle skips it)
+    const double y2 = y * y;
+    const double mr3 = (mj * y) * y2;
+    const double c = (rv * y2) * (-3.0);
+    s.ax = fma(mr3, dx, s.ax);
+    s.ay = fma(mr3, dy, s.ay);
+    s.az = fma(mr3, dz, s.az);
+    s.jx = fma(mr3, fma(c, dx, dvx), s.jx);
+    s.jy = fma(mr3, fma(c, dy, dvy), s.jy);
+    s.jz = fma(mr3, fma(c, dz, dvz), s.jz);
+}
+
+}  // namespace gdy

@@ -1,0 +1,503 @@
+// gdy_step.cuh — the rest of the block-timestep step on the device: predictor, save-old, partial-force
+// reduction, corrector + timestep levels, scheduler (next block time, ordered active-list compaction),
+// energy, AoS<->SoA packing, and the two measurement micro-kernels.
+//
+// Everything that decides the SCHEDULE (predictor, corrector, timestep criterion, level snapping, the
+// active-set test) is written with explicit round-to-nearest intrinsics (__dadd_rn, __dmul_rn,
+// __ddiv_rn, __dsqrt_rn): nvcc never contracts those into FMAs, so given identical forces the results
+// are bit-identical to the reference's CPU back end, which is compiled without FMA (reference:
+// src/Makefile:40-54) — the GPU back end of the reference uses different constants and is NOT followed
+// (reference: src/include/gpu/Hermite4GPU_kernels.cu:141-142, src/include/gpu/Hermite4GPU.cu:293-298).
+#pragma once
+#include "gdy_device.cuh"
+
+namespace gdy {
+
+constexpr double D_TIME_MIN = 1.1920928955078125e-07;  // 2^-23, reference: src/include/common.hpp:120
+constexpr double D_TIME_MAX = 0.125;                   // 2^-3,  reference: src/include/common.hpp:126
+constexpr double DBL_EPS2 = 2.0 * 2.220446049250313e-16;  // 2*epsilon, reference: Hermite4.cpp:76-77
+
+__device__ __forceinline__ double mul(double a, double b) { return __dmul_rn(a, b); }
+__device__ __forceinline__ double add(double a, double b) { return __dadd_rn(a, b); }
+__device__ __forceinline__ double sub(double a, double b) { return __dsub_rn(a, b); }
+__device__ __forceinline__ double dvd(double a, double b) { return __ddiv_rn(a, b); }
+
+// Taylor predictor of one particle.  Expression order of Hermite4CPU::predicted_pos_vel
+// (reference: src/include/cpu/Hermite4CPU.cpp:346-359): dt2 = dt*dt, dt3 = dt2*dt, dt2/2.0, dt3/6.0,
+// ((dt3c*j + dt2c*a) + dt*v) + r and (dt2c*j + dt*a) + v.
+struct Pred6 { double x, y, z, vx, vy, vz; };
+__device__ __forceinline__ Pred6 predict_one(const State &s, uint32_t i, double itime)
+{
+    const double dt = sub(itime, s.t[i]);
+    const double dt2 = mul(dt, dt);
+    const double dt3 = mul(dt2, dt);
+    const double dt2c = dvd(dt2, 2.0);
+    const double dt3c = dvd(dt3, 6.0);
+    const double ax = s.f[0][i], ay = s.f[1][i], az = s.f[2][i];
+    const double jx = s.f[3][i], jy = s.f[4][i], jz = s.f[5][i];
+    const double vx = s.vx[i], vy = s.vy[i], vz = s.vz[i];
+    Pred6 p;
+    p.x = add(add(add(mul(dt3c, jx), mul(dt2c, ax)), mul(dt, vx)), s.x[i]);
+    p.y = add(add(add(mul(dt3c, jy), mul(dt2c, ay)), mul(dt, vy)), s.y[i]);
+    p.z = add(add(add(mul(dt3c, jz), mul(dt2c, az)), mul(dt, vz)), s.z[i]);
+    p.vx = add(add(mul(dt2c, jx), mul(dt, ax)), vx);
+    p.vy = add(add(mul(dt2c, jy), mul(dt, ay)), vy);
+    p.vz = add(add(mul(dt2c, jz), mul(dt, az)), vz);
+    return p;
+}
+
+// predicted_pos_vel(ITIME) for particles [begin, end).  Replaces k_prediction (reference:
+// src/include/gpu/Hermite4GPU_kernels.cu:127-158).
+__global__ void k_predict(State s, uint32_t begin, uint32_t end, double itime)
+{
+    const uint32_t i = begin + blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= end) return;
+    const Pred6 p = predict_one(s, i, itime);
+    s.p[0][i] = p.x; s.p[1][i] = p.y; s.p[2][i] = p.z;
+    s.p[3][i] = p.vx; s.p[4][i] = p.vy; s.p[5][i] = p.vz;
+}
+
+// init: predicted = current (reference: Hermite4::init_data, src/include/Hermite4.cpp:198-210)
+__global__ void k_copy_to_pred(State s, uint32_t npad)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= npad) return;
+    s.p[0][i] = s.x[i]; s.p[1][i] = s.y[i]; s.p[2][i] = s.z[i];
+    s.p[3][i] = s.vx[i]; s.p[4][i] = s.vy[i]; s.p[5][i] = s.vz[i];
+}
+
+// Gather the predicted pos/vel of the active list into k-indexed arrays (the i-particles of the force
+// kernels; replaces the host gather + H2D copy of h_i, reference: src/include/gpu/Hermite4GPU.cu:405-421)
+// and, when save_old is set, do save_old_acc_jrk for them (reference: src/include/Hermite4.cpp:145-153).
+// do_predict: the prediction of the active particle is computed here (same arithmetic as k_predict, so
+// bit-identical) and stored to p[i] as well — with the j-particles sharded over GPUs a rank only
+// predicts its own j-slice in k_predict, but the corrector needs p[i] of every active particle.
+__global__ void k_gather_active(State s, const uint32_t *__restrict__ move, uint32_t nact,
+                                int save_old, int do_predict, double itime)
+{
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= nact) return;
+    const uint32_t i = move[k];
+    if (do_predict)
+    {
+        const Pred6 p = predict_one(s, i, itime);
+        s.p[0][i] = p.x; s.p[1][i] = p.y; s.p[2][i] = p.z;
+        s.p[3][i] = p.vx; s.p[4][i] = p.vy; s.p[5][i] = p.vz;
+        s.ip[0][k] = p.x; s.ip[1][k] = p.y; s.ip[2][k] = p.z;
+        s.ip[3][k] = p.vx; s.ip[4][k] = p.vy; s.ip[5][k] = p.vz;
+    }
+    else
+    {
+#pragma unroll
+        for (int c = 0; c < 6; ++c) s.ip[c][k] = s.p[c][i];
+    }
+    if (save_old)
+    {
+#pragma unroll
+        for (int c = 0; c < 6; ++c) s.old[c][i] = s.f[c][i];
+    }
+}
+
+__global__ void k_save_old(State s, uint32_t nact)
+{
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= nact) return;
+    const uint32_t i = s.move[k];
+#pragma unroll
+    for (int c = 0; c < 6; ++c) s.old[c][i] = s.f[c][i];
+}
+
+// Sum the j-split partials in ascending split order (deterministic) -> fsum[6][nact_pad].
+// Replaces k_reduce (reference: src/include/gpu/Hermite4GPU_kernels.cu:226-248).
+// Block = 32 k-lanes x 8 split-warps: coalesced over k, the splits strided over the warps and
+// folded through shared memory in warp order.
+__global__ void __launch_bounds__(256)
+k_reduce_partials(const double *__restrict__ part, double *__restrict__ fsum, uint32_t nact,
+                  uint32_t nact_pad, uint32_t nsplit)
+{
+    __shared__ double red[8][6][32];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const uint32_t k = blockIdx.x * 32 + lane;
+    double a[6] = {0, 0, 0, 0, 0, 0};
+    if (k < nact)
+        for (uint32_t sp = w; sp < nsplit; sp += 8)
+        {
+            const double *p = part + (size_t)sp * 6 * nact_pad + k;
+#pragma unroll
+            for (int c = 0; c < 6; ++c) a[c] += p[(size_t)c * nact_pad];
+        }
+#pragma unroll
+    for (int c = 0; c < 6; ++c) red[w][c][lane] = a[c];
+    __syncthreads();
+    if (w < 6 && k < nact)
+    {
+        double sum = 0.0;
+#pragma unroll
+        for (int ww = 0; ww < 8; ++ww) sum += red[ww][w][lane];
+        fsum[(size_t)w * nact_pad + k] = sum;
+    }
+}
+
+// h_f[move[k]] = summed force (the tail of update_acc_jrk).  fbuf = [6][ld], k-indexed.
+__global__ void k_scatter_forces(State s, const uint32_t *__restrict__ move, uint32_t nact,
+                                 const double *__restrict__ fbuf, uint32_t ld)
+{
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= nact) return;
+    const uint32_t i = move ? move[k] : k;
+#pragma unroll
+    for (int c = 0; c < 6; ++c) s.f[c][i] = fbuf[(size_t)c * ld + k];
+}
+
+// ---- corrector + timestep ---------------------------------------------------------------------
+__device__ __forceinline__ double magnitude(double x, double y, double z)
+{
+    // reference: NbodyUtils::get_magnitude, src/include/utils/NbodyUtils.cpp:331-334
+    return __dsqrt_rn(add(add(mul(x, x), mul(y, y)), mul(z, z)));
+}
+
+// reference: NbodyUtils::normalize_dt, src/include/utils/NbodyUtils.cpp:371-424
+__device__ __forceinline__ double normalize_dt(double new_dt, double old_dt, double t)
+{
+    const double o8 = dvd(old_dt, 8.0), o4 = dvd(old_dt, 4.0), o2 = dvd(old_dt, 2.0);
+    if (new_dt <= o8) new_dt = D_TIME_MIN;
+    else if (o8 < new_dt && new_dt <= o4) new_dt = o8;
+    else if (o4 < new_dt && new_dt <= o2) new_dt = o4;
+    else if (o2 < new_dt && new_dt <= old_dt) new_dt = o2;
+    else if (old_dt < new_dt && new_dt <= mul(old_dt, 2.0)) new_dt = old_dt;
+    else if (mul(2.0, old_dt) < new_dt)
+    {
+        const double val = dvd(t, mul(2.0, old_dt));
+        new_dt = (ceil(val) == val) ? mul(2.0, old_dt) : old_dt;
+    }
+    else new_dt = old_dt;   // NaN falls through here, as in the reference
+
+    if (new_dt < D_TIME_MIN) new_dt = D_TIME_MIN;
+    else if (new_dt > D_TIME_MAX) new_dt = D_TIME_MAX;
+    return new_dt;
+}
+
+// correction_pos_vel(ITIME, nact) with get_timestep_normal + normalize_dt.  Expression order of the
+// CPU back end (reference: src/include/cpu/Hermite4CPU.cpp:370-411, NbodyUtils.cpp:337-365).
+// The reference runs this on the host even in its GPU build (reference: Hermite4GPU.cu:274-328).
+// fbuf != NULL: the new forces are taken from the k-indexed buffer [6][ld] the force path produced and
+// stored to h_f here (fuses the scatter at the end of update_acc_jrk into the corrector).
+__global__ void k_correct(State s, uint32_t nact, double itime, double eta,
+                          const double *__restrict__ fbuf, uint32_t ld)
+{
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= nact) return;
+    const uint32_t i = s.move[k];
+
+    const double dt1 = s.dt[i];
+    const double dt2 = mul(dt1, dt1);
+    const double dt3 = mul(dt2, dt1);
+    const double dt4 = mul(dt2, dt2);
+    const double dt5 = mul(dt4, dt1);
+    const double c4_24 = dvd(dt4, 24.0), c5_120 = dvd(dt5, 120.0), c3_6 = dvd(dt3, 6.0);
+
+    double a2[3], a3[3], fa[3], fj[3];
+#pragma unroll
+    for (int c = 0; c < 3; ++c)
+    {
+        const double oa = s.old[c][i], oj = s.old[3 + c][i];
+        if (fbuf)
+        {
+            fa[c] = fbuf[(size_t)c * ld + k];
+            fj[c] = fbuf[(size_t)(3 + c) * ld + k];
+            s.f[c][i] = fa[c];
+            s.f[3 + c][i] = fj[c];
+        }
+        else
+        {
+            fa[c] = s.f[c][i];
+            fj[c] = s.f[3 + c][i];
+        }
+        const double d = sub(oa, fa[c]);
+        // (-6*(old.a - f.a) - dt1*(4*old.a1 + 2*f.a1)) / dt2
+        a2[c] = dvd(sub(mul(-6.0, d), mul(dt1, add(mul(4.0, oj), mul(2.0, fj[c])))), dt2);
+        // (12*(old.a - f.a) + 6*dt1*(old.a1 + f.a1)) / dt3
+        a3[c] = dvd(add(mul(12.0, d), mul(mul(6.0, dt1), add(oj, fj[c]))), dt3);
+        s.a2[c][i] = a2[c];
+        s.a3[c][i] = a3[c];
+    }
+    // r = p.r + (dt4/24)*a2 + (dt5/120)*a3 ;  v = p.v + (dt3/6)*a2 + (dt4/24)*a3
+    s.x[i] = add(add(s.p[0][i], mul(c4_24, a2[0])), mul(c5_120, a3[0]));
+    s.y[i] = add(add(s.p[1][i], mul(c4_24, a2[1])), mul(c5_120, a3[1]));
+    s.z[i] = add(add(s.p[2][i], mul(c4_24, a2[2])), mul(c5_120, a3[2]));
+    s.vx[i] = add(add(s.p[3][i], mul(c3_6, a2[0])), mul(c4_24, a3[0]));
+    s.vy[i] = add(add(s.p[4][i], mul(c3_6, a2[1])), mul(c4_24, a3[1]));
+    s.vz[i] = add(add(s.p[5][i], mul(c3_6, a2[2])), mul(c4_24, a3[2]));
+    s.t[i] = itime;
+
+    // get_timestep_normal(i, eta): h_dt[i] is still the old step here
+    const double ax1_2 = add(a2[0], mul(dt1, a3[0]));
+    const double ay1_2 = add(a2[1], mul(dt1, a3[1]));
+    const double az1_2 = add(a2[2], mul(dt1, a3[2]));
+    const double abs_a1 = magnitude(fa[0], fa[1], fa[2]);
+    const double abs_j1 = magnitude(fj[0], fj[1], fj[2]);
+    const double abs_j12 = mul(abs_j1, abs_j1);
+    const double abs_a1_3 = magnitude(a3[0], a3[1], a3[2]);
+    const double abs_a1_2 = magnitude(ax1_2, ay1_2, az1_2);
+    const double abs_a1_22 = mul(abs_a1_2, abs_a1_2);
+    const double normal_dt = __dsqrt_rn(
+        mul(eta, dvd(add(mul(abs_a1, abs_a1_2), abs_j12), add(mul(abs_j1, abs_a1_3), abs_a1_22))));
+    s.dt[i] = normalize_dt(normal_dt, dt1, itime);
+}
+
+// ---- scheduler -----------------------------------------------------------------------------------
+// next_integration_time: min over all particles of t+dt (reference: src/include/Hermite4.cpp:90-102),
+// in two phases without atomics: k_min_time leaves one minimum per block, the consumer (k_sched_count /
+// k_sched_write / k_min_final) folds the <= MIN_BLOCKS block minima itself.  fmin is exact and
+// order-independent, so every block (and every GPU) gets the same bit pattern.
+constexpr int MIN_BLOCKS = 256;
+
+__device__ __forceinline__ double block_min_256(double m, double *sm /* [8] */)
+{
+#pragma unroll
+    for (int off = 16; off; off >>= 1) m = fmin(m, __shfl_xor_sync(0xffffffffu, m, off));
+    __syncthreads();   // protect sm from a previous use
+    if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = m;
+    __syncthreads();
+    m = sm[0];
+#pragma unroll
+    for (int w = 1; w < 8; ++w) m = fmin(m, sm[w]);
+    return m;
+}
+
+__global__ void __launch_bounds__(256)
+k_min_time(State s, uint32_t n, double *__restrict__ block_min)
+{
+    __shared__ double sm[8];
+    double m = __longlong_as_double(0x7ff0000000000000LL);
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+        m = fmin(m, add(s.t[i], s.dt[i]));
+    m = block_min_256(m, sm);
+    if (threadIdx.x == 0) block_min[blockIdx.x] = m;
+}
+
+// fold the block minima (called by all 256 threads of a block)
+__device__ __forceinline__ double fold_block_min(const double *__restrict__ block_min, uint32_t nmin,
+                                                 double *sm)
+{
+    double m = __longlong_as_double(0x7ff0000000000000LL);
+    if (threadIdx.x < nmin) m = block_min[threadIdx.x];
+    return block_min_256(m, sm);
+}
+
+__global__ void __launch_bounds__(256)
+k_min_final(const double *__restrict__ block_min, uint32_t nmin, double *atime_dev, double *atime_host)
+{
+    __shared__ double sm[8];
+    const double m = fold_block_min(block_min, nmin, sm);
+    if (threadIdx.x == 0)
+    {
+        *atime_dev = m;
+        if (atime_host) *atime_host = m;
+    }
+}
+
+// find_particles_to_move(ITIME): ordered compaction, two passes over chunks of 1024 particles.
+// Active test of the reference: fabs(ITIME - (t+dt)) < 2*epsilon (src/include/Hermite4.cpp:75-77).
+// block_min != NULL: ITIME is the minimum left by k_min_time (the next block time), so the scheduler
+// of step k+1 chains behind the corrector of step k without a host round trip.
+constexpr int SCHED_ITEMS = 4;
+constexpr int SCHED_BLOCK = 256;
+constexpr int SCHED_CHUNK = SCHED_ITEMS * SCHED_BLOCK;
+
+__device__ __forceinline__ bool is_active(const State &s, uint32_t i, uint32_t n, double itime)
+{
+    if (i >= n) return false;
+    const double tmp_time = add(s.t[i], s.dt[i]);
+    return fabs(sub(itime, tmp_time)) < DBL_EPS2;
+}
+
+__global__ void __launch_bounds__(SCHED_BLOCK)
+k_sched_count(State s, uint32_t n, double itime, const double *__restrict__ block_min, uint32_t nmin,
+              uint32_t *__restrict__ block_cnt)
+{
+    __shared__ double sm[8];
+    __shared__ int wsum[SCHED_BLOCK / 32];
+    if (block_min) itime = fold_block_min(block_min, nmin, sm);
+    const uint32_t base = blockIdx.x * SCHED_CHUNK + threadIdx.x * SCHED_ITEMS;
+    int v = 0;
+#pragma unroll
+    for (int e = 0; e < SCHED_ITEMS; ++e) v += is_active(s, base + e, n, itime) ? 1 : 0;
+#pragma unroll
+    for (int off = 16; off; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
+    if ((threadIdx.x & 31) == 0) wsum[threadIdx.x >> 5] = v;
+    __syncthreads();
+    if (threadIdx.x == 0)
+    {
+        int b = 0;
+#pragma unroll
+        for (int w = 0; w < SCHED_BLOCK / 32; ++w) b += wsum[w];
+        block_cnt[blockIdx.x] = (uint32_t)b;
+    }
+}
+
+// out2_host (pinned, may be NULL) receives {ITIME bits, nact}: the one readback per block step.
+struct SchedOut { double itime; uint32_t nact; uint32_t seq; };
+
+__global__ void __launch_bounds__(SCHED_BLOCK)
+k_sched_write(State s, uint32_t n, double itime, const double *__restrict__ block_min, uint32_t nmin,
+              const uint32_t *__restrict__ block_cnt, uint32_t nblocks, SchedOut *out_dev,
+              volatile SchedOut *out_host, uint32_t seq)
+{
+    __shared__ double sm[8];
+    __shared__ uint32_t sh[SCHED_BLOCK / 32];
+    __shared__ uint32_t wb[SCHED_BLOCK / 32], wt[SCHED_BLOCK / 32];
+    if (block_min) itime = fold_block_min(block_min, nmin, sm);
+    // (1) offset of this block = sum of the counts of the blocks before it (and the grand total)
+    uint32_t before = 0, total = 0;
+    for (uint32_t b = threadIdx.x; b < nblocks; b += SCHED_BLOCK)
+    {
+        const uint32_t c = block_cnt[b];
+        total += c;
+        if (b < blockIdx.x) before += c;
+    }
+#pragma unroll
+    for (int off = 16; off; off >>= 1)
+    {
+        before += __shfl_xor_sync(0xffffffffu, before, off);
+        total += __shfl_xor_sync(0xffffffffu, total, off);
+    }
+    if ((threadIdx.x & 31) == 0) { wb[threadIdx.x >> 5] = before; wt[threadIdx.x >> 5] = total; }
+    // (2) flags of my items, exclusive scan inside the block, ordered write
+    const uint32_t base = blockIdx.x * SCHED_CHUNK + threadIdx.x * SCHED_ITEMS;
+    bool fl[SCHED_ITEMS];
+    uint32_t c = 0;
+#pragma unroll
+    for (int e = 0; e < SCHED_ITEMS; ++e) { fl[e] = is_active(s, base + e, n, itime); c += fl[e] ? 1u : 0u; }
+    uint32_t incl = c;
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1)
+    {
+        const uint32_t v = __shfl_up_sync(0xffffffffu, incl, off);
+        if (lane >= off) incl += v;
+    }
+    if (lane == 31) sh[w] = incl;
+    __syncthreads();
+    uint32_t s_off = 0, s_tot = 0;
+#pragma unroll
+    for (int ww = 0; ww < SCHED_BLOCK / 32; ++ww) { s_off += wb[ww]; s_tot += wt[ww]; }
+    if (blockIdx.x == 0 && threadIdx.x == 0)
+    {
+        out_dev->itime = itime; out_dev->nact = s_tot; out_dev->seq = seq;
+        if (out_host)
+        {
+            out_host->itime = itime; out_host->nact = s_tot;
+            __threadfence_system();
+            out_host->seq = seq;   // written last: the host may poll on it
+        }
+    }
+    uint32_t woff = 0;
+    for (int ww = 0; ww < w; ++ww) woff += sh[ww];
+    uint32_t pos = s_off + woff + incl - c;
+#pragma unroll
+    for (int e = 0; e < SCHED_ITEMS; ++e)
+        if (fl[e]) s.move[pos++] = base + e;
+}
+
+// ---- energy ------------------------------------------------------------------------------------------
+// Kinetic 0.5 m v^2 and UNSOFTENED potential -sum_{i<j} m_i m_j / r_ij (reference:
+// src/include/utils/NbodyUtils.cpp:427-529; k_energy, src/include/gpu/Hermite4GPU_kernels.cu:250-288).
+// The reference's triangular j>i loop is load-imbalanced; here every i sums over all j != i on a
+// shared-memory tile and the result is halved.
+__global__ void __launch_bounds__(128)
+k_energy(State s, uint32_t n, uint32_t npad, double *__restrict__ ekin, double *__restrict__ epot)
+{
+    __shared__ double sx[128], sy[128], sz[128], smass[128];
+    const uint32_t i = blockIdx.x * 128 + threadIdx.x;
+    const uint32_t ic = i < n ? i : n - 1;
+    const double xi = s.x[ic], yi = s.y[ic], zi = s.z[ic];
+    double pot = 0.0;
+    for (uint32_t t = 0; t < npad; t += 128)
+    {
+        __syncthreads();
+        sx[threadIdx.x] = s.x[t + threadIdx.x];
+        sy[threadIdx.x] = s.y[t + threadIdx.x];
+        sz[threadIdx.x] = s.z[t + threadIdx.x];
+        smass[threadIdx.x] = s.m[t + threadIdx.x];
+        __syncthreads();
+#pragma unroll 4
+        for (int j = 0; j < 128; ++j)
+        {
+            const double dx = sx[j] - xi, dy = sy[j] - yi, dz = sz[j] - zi;
+            const double r2 = fma(dz, dz, fma(dy, dy, dx * dx));
+            double y = rsqrt_f64(r2);
+            y = (r2 > 0.0) ? y : 0.0;   // i == j
+            pot = fma(smass[j], y, pot);
+        }
+    }
+    if (i < n)
+    {
+        const double mi = s.m[i];
+        const double vx = s.vx[i], vy = s.vy[i], vz = s.vz[i];
+        ekin[i] = 0.5 * mi * (vx * vx + vy * vy + vz * vz);
+        epot[i] = -0.5 * mi * pot;
+    }
+}
+
+// Deterministic sum of two arrays (fixed tree): out[0] = sum a, out[1] = sum b.  One block.
+__global__ void __launch_bounds__(1024) k_sum2(const double *a, const double *b, uint32_t n, double *out)
+{
+    __shared__ double sa[1024], sb[1024];
+    double x = 0.0, y = 0.0;
+    for (uint32_t i = threadIdx.x; i < n; i += 1024) { x += a[i]; y += b[i]; }
+    sa[threadIdx.x] = x; sb[threadIdx.x] = y;
+    __syncthreads();
+    for (int off = 512; off; off >>= 1)
+    {
+        if ((int)threadIdx.x < off) { sa[threadIdx.x] += sa[threadIdx.x + off]; sb[threadIdx.x] += sb[threadIdx.x + off]; }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) { out[0] = sa[0]; out[1] = sb[0]; }
+}
+
+// ---- AoS <-> SoA packing ------------------------------------------------------------------------
+// aos[i*stride + c] <-> col[c][i]
+struct Cols { double *c[8]; };
+__global__ void k_unpack(const double *__restrict__ aos, Cols cols, int ncol, int stride, uint32_t n)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    for (int c = 0; c < ncol; ++c)
+        if (cols.c[c]) cols.c[c][i] = aos[(size_t)i * stride + c];
+}
+__global__ void k_pack(double *__restrict__ aos, Cols cols, int ncol, int stride, uint32_t n)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    for (int c = 0; c < ncol; ++c) aos[(size_t)i * stride + c] = cols.c[c] ? cols.c[c][i] : 0.0;
+}
+__global__ void k_fill(double *p, double v, uint32_t begin, uint32_t end)
+{
+    const uint32_t i = begin + blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < end) p[i] = v;
+}
+
+// ---- measurement micro-kernels (roofline denominators; not on the hot path) -------------------------
+// 8 independent DFMA chains per thread: the FP64 pipe's issue rate, nothing else.
+__global__ void __launch_bounds__(256) k_dfma_peak(double *out, int iters, double a, double b,
+                                                    long long *cycles)
+{
+    double x0 = threadIdx.x, x1 = x0 + 1, x2 = x0 + 2, x3 = x0 + 3, x4 = x0 + 4, x5 = x0 + 5,
+           x6 = x0 + 6, x7 = x0 + 7;
+    const long long c0 = clock64();
+    for (int it = 0; it < iters; ++it)
+    {
+#pragma unroll
+        for (int u = 0; u < 8; ++u)
+        {
+            x0 = fma(x0, a, b); x1 = fma(x1, a, b); x2 = fma(x2, a, b); x3 = fma(x3, a, b);
+            x4 = fma(x4, a, b); x5 = fma(x5, a, b); x6 = fma(x6, a, b); x7 = fma(x7, a, b);
+        }
+    }
+    const long long c1 = clock64();
+    out[blockIdx.x * blockDim.x + threadIdx.x] = ((x0 + x1) + (x2 + x3)) + ((x4 + x5) + (x6 + x7));
+    if (blockIdx.x == 0 && threadIdx.x == 0) *cycles = c1 - c0;
+}
+
+}  // namespace gdy

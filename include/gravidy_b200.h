@@ -1,0 +1,164 @@
+/* gravidy_b200.h — C ABI of the B200-native Hermite4 hot path.
+ *
+ * One `gdy_ctx` = one GPU (one j-shard).  It owns the device-resident particle state, streams and
+ * (when world > 1) an NCCL communicator.  The entry points are the hooks the reference's
+ * integration loop calls (reference: src/include/cpu/Hermite4CPU_integration.cpp:81-124, identical
+ * in src/include/gpu/Hermite4GPU_integration.cpp:81-124); each one replaces the Hermite4GPU
+ * member cited beside it.  Plain pointers and sizes only; no C++/torch types cross this boundary.
+ *
+ * Conventions
+ *   - every call returns 0 on success, a negative gdy_status on error; gdy_last_error(ctx) gives
+ *     the message.  (The reference's convention is print + exit(EXIT_FAILURE), reference:
+ *     src/include/gpu/Hermite4GPU.cuh:43-50; the host shim in gravidy_b200/host keeps it.)
+ *   - host pointers are borrowed for the duration of the call.
+ *   - one caller thread per context (like the reference); calls are stream-ordered; only the calls
+ *     that return a value to the host synchronise.
+ *   - array shapes follow the reference's host arrays: r4 = N x {x,y,z,m} (double4 h_r), v4 = N x
+ *     {x,y,z,_} (double4 h_v), f6 = N x {a[3],a1[3]} (Forces), a3x3 = N x {x,y,z} (double3).
+ *   - there is NO CPU fallback: without a CUDA device gdy_create fails with GDY_ERR_NO_DEVICE.
+ */
+#ifndef GRAVIDY_B200_H
+#define GRAVIDY_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct gdy_ctx gdy_ctx;
+
+typedef enum gdy_status
+{
+    GDY_OK = 0,
+    GDY_ERR_INVALID = -1,   /* bad argument */
+    GDY_ERR_NO_DEVICE = -2, /* no usable CUDA device: there is no CPU path */
+    GDY_ERR_CUDA = -3,      /* CUDA runtime error, see gdy_last_error */
+    GDY_ERR_NCCL = -4,      /* NCCL error or libnccl not loadable */
+    GDY_ERR_STATE = -5      /* call sequence error (e.g. no particles uploaded) */
+} gdy_status;
+
+#define GDY_NCCL_UID_BYTES 128
+
+/* Version of this ABI (bumped on any signature change). */
+int gdy_abi_version(void);
+
+/* ---- lifetime ------------------------------------------------------------------------------
+ * Replaces Hermite4GPU::Hermite4GPU / alloc_arrays_device / ~Hermite4GPU
+ * (reference: src/include/gpu/Hermite4GPU.cu:43-194).
+ *   n       particle count
+ *   e2      softening squared, as NbodySystem computes it (float product widened,
+ *           reference: src/include/NbodySystem.cpp:50)
+ *   eta     accuracy parameter, FLOAT as in the reference (src/include/NbodySystem.hpp:67)
+ *   device  CUDA device ordinal for this context
+ */
+int gdy_create(gdy_ctx **out, uint32_t n, double e2, float eta, int device);
+
+/* Sharded variant: this context is rank `rank` of `world` j-shards (contiguous equal slices,
+ * reference partition: src/include/gpu/Hermite4GPU.cu:81-97).  State is replicated; partial forces
+ * are summed with ncclAllReduce (replaces the host-side sum, reference: Hermite4GPU.cu:512-530).
+ * nccl_uid: GDY_NCCL_UID_BYTES bytes from gdy_nccl_unique_id() on rank 0, distributed by the
+ * caller (MPI, torch.distributed, a file, ...).  world == 1 ignores it (may be NULL). */
+int gdy_create_sharded(gdy_ctx **out, uint32_t n, double e2, float eta, int device, int rank,
+                       int world, const uint8_t *nccl_uid);
+int gdy_nccl_unique_id(uint8_t *uid_out /* GDY_NCCL_UID_BYTES */);
+int gdy_destroy(gdy_ctx *ctx);
+const char *gdy_last_error(const gdy_ctx *ctx); /* ctx may be NULL: last create() error */
+
+/* ---- state transfer ---------------------------------------------------------------------------
+ * Replaces the per-step cudaMemcpy of the whole particle set (reference: Hermite4GPU.cu:226-265,
+ * 338-346): state goes up once and comes down only at output points. */
+int gdy_upload_particles(gdy_ctx *ctx, const double *r4, const double *v4);
+int gdy_upload_times(gdy_ctx *ctx, const double *t, const double *dt); /* after host init_dt */
+int gdy_upload_forces(gdy_ctx *ctx, const double *f6);                 /* tests / resume     */
+int gdy_download_forces(gdy_ctx *ctx, double *f6);
+/* Any pointer may be NULL.  old6 = Forces h_old, a2/a3 = double3 h_a2/h_a3, p7 = N x
+ * {r[3],v[3],m} (Predictor), move = N x uint32 (entries >= nact are 0xFFFFFFFF as in the
+ * reference, src/include/Hermite4.cpp:69). */
+int gdy_download_state(gdy_ctx *ctx, double *r4, double *v4, double *f6, double *old6, double *a2,
+                       double *a3, double *t, double *dt, double *p7, uint32_t *move);
+/* Test hook: overwrite a2/a3/old on the device (NULL = keep). */
+int gdy_upload_derivs(gdy_ctx *ctx, const double *old6, const double *a2, const double *a3);
+
+/* ---- the hooks ---------------------------------------------------------------------------------- */
+/* init_acc_jrk(): all-pairs acc+jerk at the uploaded r,v.  Replaces Hermite4GPU::init_acc_jrk +
+ * k_init_acc_jrk (reference: Hermite4GPU.cu:333-375, Hermite4GPU_kernels.cu:47-87). */
+int gdy_init_acc_jrk(gdy_ctx *ctx);
+
+/* init_dt(): Aarseth initial steps on the HOST with libm log/pow exactly as the reference
+ * (src/include/Hermite4.cpp:108-140) is done by the host shim; this convenience does
+ * download_forces + that arithmetic + upload_times and returns the first block time. */
+int gdy_init_dt(gdy_ctx *ctx, float eta_s, double itime, double *atime_out);
+
+/* find_particles_to_move(ITIME): device compaction in ascending index order
+ * (reference: src/include/Hermite4.cpp:63-84). */
+int gdy_find_particles_to_move(gdy_ctx *ctx, double itime, uint32_t *nact_out);
+
+/* save_old_acc_jrk(nact) (reference: src/include/Hermite4.cpp:145-153). */
+int gdy_save_old_acc_jrk(gdy_ctx *ctx, uint32_t nact);
+
+/* predicted_pos_vel(ITIME): replaces Hermite4GPU::predicted_pos_vel + k_prediction (reference:
+ * Hermite4GPU.cu:201-268, Hermite4GPU_kernels.cu:127-158) with the CPU back end's expression order
+ * (src/include/cpu/Hermite4CPU.cpp:340-365). */
+int gdy_predicted_pos_vel(gdy_ctx *ctx, double itime);
+
+/* update_acc_jrk(nact): replaces Hermite4GPU::update_acc_jrk + k_update + k_reduce + the host sum
+ * (reference: Hermite4GPU.cu:385-535, Hermite4GPU_kernels.cu:165-248).  With world > 1 includes the
+ * NCCL allreduce. */
+int gdy_update_acc_jrk(gdy_ctx *ctx, uint32_t nact);
+
+/* correction_pos_vel(ITIME, nact) incl. get_timestep_normal + normalize_dt (reference:
+ * src/include/cpu/Hermite4CPU.cpp:370-411, src/include/utils/NbodyUtils.cpp:337-424). */
+int gdy_correction_pos_vel(gdy_ctx *ctx, double itime, uint32_t nact);
+
+/* next_integration_time(ATIME) (reference: src/include/Hermite4.cpp:90-102). */
+int gdy_next_integration_time(gdy_ctx *ctx, double *atime_out);
+
+/* get_energy_gpu() + k_energy (reference: Hermite4GPU.cu:540-592, Hermite4GPU_kernels.cu:250-288;
+ * CPU: src/include/utils/NbodyUtils.cpp:427-529).  Unsoftened potential. */
+int gdy_energy(gdy_ctx *ctx, double *ekin_out, double *epot_out);
+
+/* ---- fused drivers (same arithmetic as the hooks, fewer launches / host round trips) -------------- */
+typedef struct gdy_run_stats
+{
+    uint64_t iterations;   /* block steps done in this call          */
+    uint64_t nsteps;       /* sum of nact                            */
+    uint64_t interactions; /* sum of nact * n, 64-bit                */
+    double itime;          /* ITIME of the last completed block step */
+    double atime;          /* next block time                        */
+    double force_ms;       /* device time in the force kernels       */
+    double wall_ms;        /* host wall time of the call             */
+} gdy_run_stats;
+
+/* Runs the reference loop body (find -> save_old -> predict -> update -> correct -> next time)
+ * until ITIME >= t_stop or max_steps block steps (0 = unlimited).  atime = the next block time
+ * (from gdy_init_dt or the previous call).  trace_nact/trace_itime (may be NULL) receive the first
+ * trace_cap steps. */
+int gdy_run(gdy_ctx *ctx, double atime, double itime0, double t_stop, uint64_t max_steps,
+            gdy_run_stats *stats, uint32_t *trace_nact, double *trace_itime, uint64_t trace_cap);
+
+/* ---- bench / test entry points ---------------------------------------------------------------------- */
+/* Forces of an explicit active list on the current PREDICTED positions (call predicted_pos_vel or
+ * init first).  move = nact indices; f6_out (may be NULL) = nact x 6.  *ms_out (may be NULL) = device
+ * time of the force kernels (CUDA events on the launching stream). */
+int gdy_force_sweep(gdy_ctx *ctx, uint32_t nact, const uint32_t *move, double *f6_out,
+                    float *ms_out);
+/* Same, nact = n, identity list, no host traffic: `reps` back-to-back evaluations, mean ms. */
+int gdy_force_sweep_full(gdy_ctx *ctx, int reps, float *ms_out);
+
+/* Force-kernel variant override for tuning (-1 = heuristic). */
+int gdy_set_tuning(gdy_ctx *ctx, int variant, int jsplit);
+
+/* Measured denominators for the roofline (measurement infrastructure, not the hot path):
+ * dependent-free DFMA loop on every SM -> TFLOP/s (2 flop per DFMA), and a device copy -> GB/s. */
+int gdy_measure_fp64_peak(gdy_ctx *ctx, double *tflops_out, double *sm_mhz_out);
+int gdy_measure_copy_bw(gdy_ctx *ctx, double *gbs_out);
+
+/* Number of kernels this context has launched (bench.py's gpu_launches). */
+uint64_t gdy_launch_count(const gdy_ctx *ctx);
+int gdy_sync(gdy_ctx *ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GRAVIDY_B200_H */

@@ -1,0 +1,256 @@
+"""GPU parity suite (-m gpu): the CUDA path, called through the C ABI, against the CPU oracle.
+
+Tolerances (BASELINE.json north_star): per-particle acc/jerk within 1e-12 relative (2-norm of the
+difference over 2-norm of the vector); predictor, corrector, timestep levels, active sets and next block
+time BIT-EXACT given identical inputs; energy within 1e-12 relative.
+"""
+import os
+
+import numpy as np
+import pytest
+
+from gravidy_b200.plummer import plummer, default_seed
+
+pytestmark = pytest.mark.gpu
+
+FORCE_RTOL = 1e-12
+STEP_FIXTURES = ["plummer_n97_steps", "salpeter_n200_steps"]
+
+
+@pytest.fixture(scope="module")
+def H():
+    from gravidy_b200.hermite4 import Hermite4B200
+    return Hermite4B200
+
+
+@pytest.fixture(scope="module")
+def O():
+    from oracle import oracle
+    oracle.build()
+    return oracle
+
+
+def rel_err(f_gpu, f_ref):
+    """max over particles of |d acc|/|acc| and |d jerk|/|jerk| (2-norms)."""
+    da = np.linalg.norm(f_gpu[:, :3] - f_ref[:, :3], axis=1) / np.linalg.norm(f_ref[:, :3], axis=1)
+    dj = np.linalg.norm(f_gpu[:, 3:] - f_ref[:, 3:], axis=1) / np.linalg.norm(f_ref[:, 3:], axis=1)
+    return float(da.max()), float(dj.max())
+
+
+def _load(golden_dir, name):
+    return np.load(os.path.join(golden_dir, name + ".npz"))
+
+
+# ---- forces -------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name", STEP_FIXTURES)
+def test_init_acc_jrk_vs_reference_fixture(H, golden_dir, name):
+    g = _load(golden_dir, name)
+    h = H(g["m"], g["r"], g["v"], softening=float(g["softening"]), eta=float(g["eta"]))
+    assert h.e2 == float(g["e2"])
+    h.init_acc_jrk()
+    ea, ej = rel_err(h.download_forces(), g["init_f6"])
+    assert ea < FORCE_RTOL and ej < FORCE_RTOL, (ea, ej)
+    # init_dt: host libm arithmetic as the reference; levels must be identical
+    atime = h.init_dt(0.0)
+    st = h.get_state("t", "dt")
+    assert np.array_equal(st["dt"], g["init_dt"])
+    assert atime == float(g["init_atime"])
+    e = h.get_energy()
+    np.testing.assert_allclose(e, g["e0"], rtol=1e-12)
+
+
+@pytest.mark.parametrize("n,spectrum", [(1, "equal"), (2, "equal"), (33, "equal"), (255, "salpeter"),
+                                        (256, "equal"), (257, "equal"), (1024, "equal"),
+                                        (4099, "salpeter"), (16384, "equal")])
+def test_init_acc_jrk_vs_oracle(H, O, n, spectrum):
+    m, r, v = plummer(n, seed=default_seed(n), mass_spectrum=spectrum)
+    o = O.best_oracle(m, r, v) if n > 1 else O.PortOracle(m, r, v)
+    o.init_acc_jrk()
+    ref = o.get_state("f6")["f6"]
+    h = H(m, r, v)
+    h.init_acc_jrk()
+    got = h.download_forces()
+    if n == 1:
+        assert np.array_equal(got, np.zeros((1, 6)))   # self pair contributes exactly +0
+        return
+    ea, ej = rel_err(got, ref)
+    assert ea < FORCE_RTOL and ej < FORCE_RTOL, (n, ea, ej)
+
+
+def test_every_force_variant_matches_oracle(H, O):
+    """Each kernel variant (tile and lane families) on active lists of awkward sizes."""
+    n = 3001
+    m, r, v = plummer(n, seed=5, mass_spectrum="salpeter")
+    o = O.PortOracle(m, r, v)
+    o.init_acc_jrk()
+    ref = o.get_state("f6")["f6"]
+    h = H(m, r, v)
+    h.init_acc_jrk()
+    rng = np.random.default_rng(0)
+    nvariants = 12
+    for variant in range(nvariants):
+        for nact in (1, 2, 3, 17, 31, 100, 513, 3001):
+            for jsplit in (-1, 1, 5):
+                move = np.sort(rng.choice(n, size=nact, replace=False)).astype(np.uint32)
+                h.set_tuning(variant, jsplit)
+                got, _ = h.force_sweep(move)
+                ea, ej = rel_err(got, ref[move])
+                assert ea < FORCE_RTOL and ej < FORCE_RTOL, (variant, nact, jsplit, ea, ej)
+    h.set_tuning(-1, -1)
+
+
+def test_zero_softening_masks_self_pair(H, O):
+    n = 300
+    m, r, v = plummer(n, seed=9)
+    o = O.PortOracle(m, r, v, softening=0.0)
+    o.init_acc_jrk()
+    ref = o.get_state("f6")["f6"]
+    h = H(m, r, v, softening=0.0)
+    assert h.e2 == 0.0
+    h.init_acc_jrk()
+    got = h.download_forces()
+    assert np.isfinite(got).all()
+    ea, ej = rel_err(got, ref)
+    assert ea < FORCE_RTOL and ej < FORCE_RTOL
+
+
+# ---- one block step, hook by hook --------------------------------------------------------------------
+@pytest.mark.parametrize("name", STEP_FIXTURES)
+def test_block_step_hooks_vs_reference_fixture(H, golden_dir, name):
+    g = _load(golden_dir, name)
+    h = H(g["m"], g["r"], g["v"], softening=float(g["softening"]), eta=float(g["eta"]))
+    h.set_state(r4=g["pre_r4"], v4=g["pre_v4"], f6=g["pre_f6"], old6=g["pre_old6"], a2=g["pre_a2"],
+                a3=g["pre_a3"], t=g["pre_t"], dt=g["pre_dt"])
+    itime = float(g["itime"][-1])
+    nact = h.find_particles_to_move(itime)
+    assert nact == int(g["nact"][-1])
+    assert np.array_equal(h.get_state("move")["move"], g["pre_move"])
+    h.save_old_acc_jrk(nact)
+    h.predicted_pos_vel(itime)
+    assert np.array_equal(h.get_state("p7")["p7"], g["last_p7"])            # bit-exact predictor
+    h.update_acc_jrk(nact)
+    f = h.get_state("f6")["f6"]
+    mv = g["pre_move"][:nact]
+    ea, ej = rel_err(f[mv], g["last_f6"][mv])
+    assert ea < FORCE_RTOL and ej < FORCE_RTOL
+    inactive = np.setdiff1d(np.arange(len(f)), mv)
+    assert np.array_equal(f[inactive], g["last_f6"][inactive])              # untouched
+    # identical forces in -> corrector, timestep levels and next block time bit-exact out
+    h.upload_forces(g["last_f6"])
+    h.correction_pos_vel(itime, nact)
+    post = h.get_state()
+    for k in ("r4", "v4", "f6", "old6", "a2", "a3", "t", "dt"):
+        assert np.array_equal(post[k], g["post_" + k]), k
+    assert h.next_integration_time() == float(g["final_atime"])
+
+
+@pytest.mark.parametrize("name", STEP_FIXTURES)
+def test_hook_loop_schedule_vs_reference_fixture(H, golden_dir, name):
+    """The reference loop driven hook by hook from t=0: same active-set sizes and block times."""
+    g = _load(golden_dir, name)
+    h = H(g["m"], g["r"], g["v"], softening=float(g["softening"]), eta=float(g["eta"]))
+    h.init_acc_jrk()
+    atime = h.init_dt(0.0)
+    for s in range(len(g["nact"])):
+        itime = atime
+        nact = h.find_particles_to_move(itime)
+        assert (nact, itime) == (int(g["nact"][s]), float(g["itime"][s])), s
+        h.save_old_acc_jrk(nact)
+        h.predicted_pos_vel(itime)
+        h.update_acc_jrk(nact)
+        h.correction_pos_vel(itime, nact)
+        atime = h.next_integration_time()
+    assert atime == float(g["final_atime"])
+    post = h.get_state("r4", "v4", "dt", "t")
+    assert np.array_equal(post["dt"], g["post_dt"]) and np.array_equal(post["t"], g["post_t"])
+    np.testing.assert_allclose(post["r4"], g["post_r4"], rtol=0, atol=1e-11)
+    np.testing.assert_allclose(post["v4"], g["post_v4"], rtol=0, atol=1e-10)
+    np.testing.assert_allclose(h.get_energy(), g["e1"], rtol=1e-10)
+
+
+@pytest.mark.parametrize("name", STEP_FIXTURES)
+def test_fused_run_equals_hook_loop(H, golden_dir, name):
+    """gdy_run (chained scheduler, fused gather/save-old and scatter/corrector) == the hook sequence."""
+    g = _load(golden_dir, name)
+    nsteps = len(g["nact"])
+    h = H(g["m"], g["r"], g["v"], softening=float(g["softening"]), eta=float(g["eta"]))
+    h.init_acc_jrk()
+    atime = h.init_dt(0.0)
+    st, tn, ti = h.run(atime, 1e9, max_steps=nsteps, trace_cap=nsteps)
+    assert st.iterations == nsteps
+    assert np.array_equal(tn, g["nact"]) and np.array_equal(ti, g["itime"])
+    assert st.atime == float(g["final_atime"])
+    assert st.interactions == int(g["nact"].astype(np.uint64).sum()) * len(g["m"])
+    a = h.get_state()
+    h2 = H(g["m"], g["r"], g["v"], softening=float(g["softening"]), eta=float(g["eta"]))
+    h2.init_acc_jrk()
+    at = h2.init_dt(0.0)
+    for s in range(nsteps):
+        nact = h2.find_particles_to_move(at)
+        h2.save_old_acc_jrk(nact); h2.predicted_pos_vel(at); h2.update_acc_jrk(nact)
+        h2.correction_pos_vel(at, nact)
+        at = h2.next_integration_time()
+    b = h2.get_state()
+    for k in ("r4", "v4", "f6", "old6", "a2", "a3", "t", "dt", "move"):
+        assert np.array_equal(a[k], b[k]), k
+
+
+# ---- integration to t = 1 (BASELINE configs[0]) ------------------------------------------------------
+def test_run_n1024_to_t1_vs_reference_fixture(H, golden_dir):
+    g = _load(golden_dir, "plummer_n1024_t1_eps1e-2")
+    m, r, v = plummer(int(g["n"]), seed=int(g["seed"]))
+    h = H(m, r, v, softening=float(g["softening"]), eta=float(g["eta"]))
+    h.init_acc_jrk()
+    atime = h.init_dt(0.0)
+    e0 = h.get_energy()
+    np.testing.assert_allclose(e0, g["e0"], rtol=1e-12)
+    st, tn, _ = h.run(atime, float(g["t_end"]), trace_cap=1 << 16)
+    e1 = h.get_energy()
+    assert st.itime == float(g["itime"])
+    # the schedule is chaotic in the last bits of the forces: same to within a fraction of a percent
+    assert abs(int(st.iterations) - int(g["iterations"])) <= 0.01 * int(g["iterations"])
+    assert abs(int(st.nsteps) - int(g["nsteps"])) <= 0.01 * int(g["nsteps"])
+    k = 200   # ...and identical over the first few hundred block steps
+    assert np.array_equal(tn[:k], g["nact"][:k])
+    err_gpu = abs((e1[0] - e0[0]) / e0[0])
+    err_ref = abs((g["e1"][0] - g["e0"][0]) / g["e0"][0])
+    assert 0.1 < err_gpu / err_ref < 10.0, (err_gpu, err_ref)   # same decade
+
+
+def test_energy_vs_oracle(H, O):
+    n = 5000
+    m, r, v = plummer(n, seed=21, mass_spectrum="salpeter")
+    o = O.PortOracle(m, r, v)
+    h = H(m, r, v)
+    np.testing.assert_allclose(h.get_energy(), o.get_energy(), rtol=1e-12)
+
+
+# ---- size-independent properties at BASELINE sizes -----------------------------------------------------
+@pytest.mark.parametrize("n", [65536, 262144])
+def test_full_size_properties(H, O, n):
+    m, r, v = plummer(n, seed=default_seed(n))
+    h = H(m, r, v)
+    h.init_acc_jrk()
+    f = h.download_forces()
+    assert np.isfinite(f).all()
+    # Newton's third law: sum_i m_i a_i = 0 and sum_i m_i j_i = 0 (to rounding)
+    scale_a = np.abs(m[:, None] * f[:, :3]).sum(axis=0)
+    scale_j = np.abs(m[:, None] * f[:, 3:]).sum(axis=0)
+    assert (np.abs((m[:, None] * f[:, :3]).sum(axis=0)) / scale_a < 1e-11).all()
+    assert (np.abs((m[:, None] * f[:, 3:]).sum(axis=0)) / scale_j < 1e-11).all()
+    # a random subset against the oracle (update_acc_jrk-style evaluation on the CPU)
+    rng = np.random.default_rng(1)
+    move = np.sort(rng.choice(n, size=64, replace=False)).astype(np.uint32)
+    o = O.PortOracle(m, r, v)
+    o.timed_update(move)
+    ref = o.get_state("f6")["f6"][move]
+    ea, ej = rel_err(f[move], ref)
+    assert ea < FORCE_RTOL and ej < FORCE_RTOL
+    # the same subset through the small-block path must agree with the full sweep
+    got, _ = h.force_sweep(move)
+    ea, ej = rel_err(got, ref)
+    assert ea < FORCE_RTOL and ej < FORCE_RTOL
+    # virial-equilibrium Plummer model in Henon units: E ~ -1/4
+    if n <= 65536:
+        e, ek, ep = h.get_energy()
+        assert abs(e + 0.25) < 0.02 and abs(ek / abs(ep) - 0.5) < 0.03
