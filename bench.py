@@ -251,8 +251,8 @@ def run_b200(args, m, r, v):
         st, _, _ = h.run(at, 1e9, max_steps=50)
         l1 = h.launch_count()
         barrier()
-        st, tn, _ = h.run(st.atime, 1e9, max_steps=args.integration_steps, trace_cap=args.integration_steps,
-                          itime0=st.itime)
+        st, tn, _, tu = h.run(st.atime, 1e9, max_steps=args.integration_steps,
+                              trace_cap=args.integration_steps, itime0=st.itime, trace_us=True)
         barrier()
         wall = max_over_ranks(st.wall_ms) * 1e-3
         integ = {"workload": f"block-timestep integration, Plummer N={n}, block steps 50..{50 + st.iterations}",
@@ -262,7 +262,8 @@ def run_b200(args, m, r, v):
                  "pairs": int(st.interactions), "wall_s": wall,
                  "us_per_block_step": wall / max(int(st.iterations), 1) * 1e6,
                  "gflops": st.interactions / wall * FLOP_PER_PAIR / 1e9,
-                 "launches": h.launch_count() - l1, "t_reached": st.itime}
+                 "launches": h.launch_count() - l1, "t_reached": st.itime,
+                 "us_per_block_step_nact_le_32": float(np.median(tu[tn <= 32])) if (tn <= 32).any() else None}
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -285,10 +286,11 @@ def run_b200(args, m, r, v):
             "frac_fp64_peak": gflops / 1e3 / (peak_tf * world),
             "roofline": {"bound": "fp64", "achieved": kern_tf, "peak": peak_tf, "unit": "TFLOP/s",
                          "frac": kern_tf / peak_tf, "traffic": None,
-                         "kernel": "k_force_tile<2,4,1>",
+                         "kernel": "k_force_warp<IPT=2,WI=4,WJ=1,NST=3>",
                          "peak_source": "DFMA micro-benchmark on this GPU (gdy_measure_fp64_peak); "
                                         "MEASURED_PEAKS.json has no FP64 entry",
-                         "peak_sm_mhz": peak_mhz,
+                         "peak_equiv_sm_mhz_at_64_dfma_per_clk_per_sm": peak_mhz,
+                         "nominal_peak_at_max_clock": 2.0 * 64 * 148 * 1965e6 / 1e12,
                          "flop_convention": "60 flop/pair; the kernel issues 31 FP64 instructions/pair"},
             "e2e": e2e, "gpu_launches": int(launches), "clocks": sampler.summary(),
             "integration": integ, "cpu_baseline": cpu, "wall_timed_s": wall_timed,

@@ -38,6 +38,7 @@ SIGNATURES = {
     "gdy_create": (C.c_int, [C.POINTER(_ctx), C.c_uint32, C.c_double, C.c_float, C.c_int]),
     "gdy_create_sharded": (C.c_int, [C.POINTER(_ctx), C.c_uint32, C.c_double, C.c_float, C.c_int,
                                      C.c_int, C.c_int, C.POINTER(C.c_uint8)]),
+    "gdy_shard_range": (C.c_int, [C.c_uint32, C.c_int, C.c_int, _up, _up]),
     "gdy_nccl_unique_id": (C.c_int, [C.POINTER(C.c_uint8)]),
     "gdy_destroy": (C.c_int, [_ctx]),
     "gdy_last_error": (C.c_char_p, [_ctx]),
@@ -57,7 +58,7 @@ SIGNATURES = {
     "gdy_next_integration_time": (C.c_int, [_ctx, _dp]),
     "gdy_energy": (C.c_int, [_ctx, _dp, _dp]),
     "gdy_run": (C.c_int, [_ctx, C.c_double, C.c_double, C.c_double, C.c_uint64,
-                          C.POINTER(RunStats), _up, _dp, C.c_uint64]),
+                          C.POINTER(RunStats), _up, _dp, _fp, C.c_uint64]),
     "gdy_force_sweep": (C.c_int, [_ctx, C.c_uint32, _up, _dp, _fp]),
     "gdy_force_sweep_full": (C.c_int, [_ctx, C.c_int, _fp]),
     "gdy_set_tuning": (C.c_int, [_ctx, C.c_int, C.c_int]),

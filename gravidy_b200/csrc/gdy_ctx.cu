@@ -92,8 +92,10 @@ struct gdy_ctx
 
     struct Pinned { SchedOut sched; double atime; double energy[2]; } *pin = nullptr;
 
-    uint32_t tile_begin = 0, tile_end = 0;   // this shard's j-tiles (units of TJ)
+    uint32_t blk_begin = 0, blk_end = 0;     // this shard's j-blocks (units of JB = 64 particles)
     int num_sms = 148;
+    int occ[FV_COUNT] = {};                  // resident CTAs per SM of each force variant
+    uint32_t *d_counter = nullptr;           // arrival counters of the fused last-block reduction
     int tune_variant = -1, tune_jsplit = -1;
     uint32_t seq = 0;
     uint32_t last_nact = 0;
@@ -167,8 +169,8 @@ constexpr size_t PART_MIN_DOUBLES = (size_t)8 << 20;   // 64 MiB of j-split part
 int alloc_all(gdy_ctx *c)
 {
     const size_t np = c->npad;
-    // 7 (r,m,v) + 6 f + 6 old + 3 a2 + 3 a3 + 2 (t,dt) + 6 p + 6 ip + 6 fsum
-    const size_t narr = 7 + 6 + 6 + 3 + 3 + 2 + 6 + 6 + 6;
+    // 7 (r,m,v) + 6 f + 6 old + 3 a2 + 3 a3 + 2 (t,dt) + 7 pb + 6 fsum
+    const size_t narr = 7 + 6 + 6 + 3 + 3 + 2 + 7 + 6;
     c->part_cap = 6 * np > PART_MIN_DOUBLES ? 6 * np : PART_MIN_DOUBLES;
     c->pool_doubles = narr * np + c->part_cap;
     CU(cudaMalloc(&c->pool, c->pool_doubles * sizeof(double)));
@@ -183,8 +185,7 @@ int alloc_all(gdy_ctx *c)
     for (int k = 0; k < 3; ++k) s.a2[k] = take(np);
     for (int k = 0; k < 3; ++k) s.a3[k] = take(np);
     s.t = take(np); s.dt = take(np);
-    for (int k = 0; k < 6; ++k) s.p[k] = take(np);
-    for (int k = 0; k < 6; ++k) s.ip[k] = take(np);
+    s.pb = take(7 * np);          // 128-byte aligned: every array above is a multiple of 256 doubles
     s.fsum = take(6 * np);
     s.part = take(c->part_cap);
 
@@ -192,6 +193,9 @@ int alloc_all(gdy_ctx *c)
     CU(cudaMemsetAsync(c->d_move, 0xFF, np * sizeof(uint32_t), c->st));
     s.move = c->d_move;
     CU(cudaMalloc(&c->d_ilist, np * sizeof(uint32_t)));
+    CU(cudaMalloc(&c->d_counter, np * sizeof(uint32_t)));
+    CU(cudaMemsetAsync(c->d_counter, 0, np * sizeof(uint32_t), c->st));
+    s.tile_counter = c->d_counter;
     c->n_sched_blocks = cdiv(c->n, SCHED_CHUNK);
     CU(cudaMalloc(&c->d_block_cnt, c->n_sched_blocks * sizeof(uint32_t)));
     c->n_min_blocks = cdiv(c->n, 256 * 4);
@@ -208,13 +212,19 @@ int alloc_all(gdy_ctx *c)
     const uint32_t npd = c->npad - c->n;
     if (npd)
     {
-        double *far[6] = {s.x, s.y, s.z, s.p[0], s.p[1], s.p[2]};
+        double *far[3] = {s.x, s.y, s.z};
         for (double *a : far)
         {
             k_fill<<<cdiv(npd, 256), 256, 0, c->st>>>(a, PAD_POS, c->n, c->npad);
             LAUNCHED(c);
         }
     }
+    k_init_pb<<<cdiv(c->npad, 256), 256, 0, c->st>>>(s, c->n, c->npad);
+    LAUNCHED(c);
+    CU(force_variants_prepare());
+    for (int v = 0; v < FV_COUNT; ++v)
+        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&c->occ[v], (const void *)g_variants[v].fn[0],
+                                                         g_variants[v].threads, g_variants[v].smem));
     CU(cudaStreamSynchronize(c->st));
     return 0;
 }
@@ -230,7 +240,6 @@ extern "C" int gdy_create_sharded(gdy_ctx **out, uint32_t n, double e2, float et
     if (n == 0) return fail(c, GDY_ERR_INVALID, "n must be > 0");
     if (!(e2 >= 0.0)) return fail(c, GDY_ERR_INVALID, "e2 must be >= 0");
     if (world < 1 || rank < 0 || rank >= world) return fail(c, GDY_ERR_INVALID, "bad rank/world %d/%d", rank, world);
-    if (world > 1 && !nccl_uid) return fail(c, GDY_ERR_INVALID, "world > 1 needs an NCCL unique id");
     int ndev = 0;
     cudaError_t ce = cudaGetDeviceCount(&ndev);
     if (ce != cudaSuccess || ndev == 0)
@@ -257,10 +266,10 @@ extern "C" int gdy_create_sharded(gdy_ctx **out, uint32_t n, double e2, float et
         if (rc) break;
         if ((rc = alloc_all(c))) break;
         // contiguous, tile-aligned j-shards (reference partition: src/include/gpu/Hermite4GPU.cu:81-97)
-        const uint32_t ntile = c->npad / TJ;
-        c->tile_begin = (uint32_t)((uint64_t)ntile * rank / world);
-        c->tile_end = (uint32_t)((uint64_t)ntile * (rank + 1) / world);
-        if (world > 1)
+        const uint32_t nblk = c->npad / JB;   // same arithmetic as gdy_shard_range
+        c->blk_begin = (uint32_t)((uint64_t)nblk * rank / world);
+        c->blk_end = (uint32_t)((uint64_t)nblk * (rank + 1) / world);
+        if (world > 1 && nccl_uid)
         {
             if (!nccl_load()) { rc = fail(c, GDY_ERR_NCCL, "libnccl.so.2 not loadable: %s", dlerror()); break; }
             ncclUniqueId id;
@@ -279,6 +288,19 @@ extern "C" int gdy_create_sharded(gdy_ctx **out, uint32_t n, double e2, float et
     return GDY_OK;
 }
 
+extern "C" int gdy_shard_range(uint32_t n, int rank, int world, uint32_t *begin_out, uint32_t *end_out)
+{
+    if (n == 0 || world < 1 || rank < 0 || rank >= world) return GDY_ERR_INVALID;
+    const uint32_t npad = round_up(n, PAD), nblk = npad / JB;
+    uint32_t b = (uint32_t)((uint64_t)nblk * rank / world) * JB;
+    uint32_t e = (uint32_t)((uint64_t)nblk * (rank + 1) / world) * JB;
+    if (b > n) b = n;
+    if (e > n) e = n;
+    if (begin_out) *begin_out = b;
+    if (end_out) *end_out = e;
+    return GDY_OK;
+}
+
 extern "C" int gdy_create(gdy_ctx **out, uint32_t n, double e2, float eta, int device)
 {
     return gdy_create_sharded(out, n, e2, eta, device, 0, 1, nullptr);
@@ -292,7 +314,7 @@ extern "C" int gdy_destroy(gdy_ctx *c)
     if (c->comm && g_nccl.ok) g_nccl.CommDestroy(c->comm);
     cudaFree(c->pool); cudaFree(c->d_move); cudaFree(c->d_ilist); cudaFree(c->d_block_cnt);
     cudaFree(c->d_block_min); cudaFree(c->d_sched); cudaFree(c->d_atime); cudaFree(c->d_energy);
-    cudaFree(c->d_stage);
+    cudaFree(c->d_stage); cudaFree(c->d_counter);
     if (c->pin) cudaFreeHost(c->pin);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
@@ -340,6 +362,8 @@ extern "C" int gdy_upload_particles(gdy_ctx *c, const double *r4, const double *
     int r;
     if ((r = upload_cols(c, r4, 4, 4, rc))) return r;
     if ((r = upload_cols(c, v4, 4, 4, vc))) return r;
+    k_init_pb<<<cdiv(c->npad, 256), 256, 0, c->st>>>(s, c->n, c->npad);   // mass row of the predicted set
+    LAUNCHED(c);
     c->have_particles = true;
     c->have_pred = false;
     return GDY_OK;
@@ -392,14 +416,19 @@ extern "C" int gdy_download_state(gdy_ctx *c, double *r4, double *v4, double *f6
     int r;
     double *rc[4] = {s.x, s.y, s.z, s.m};
     double *vc[4] = {s.vx, s.vy, s.vz, nullptr};
-    double *pc[7] = {s.p[0], s.p[1], s.p[2], s.p[3], s.p[4], s.p[5], s.m};
     if (r4 && (r = download_cols(c, r4, 4, 4, rc))) return r;
     if (v4 && (r = download_cols(c, v4, 4, 4, vc))) return r;
     if (f6 && (r = download_cols(c, f6, 6, 6, s.f))) return r;
     if (old6 && (r = download_cols(c, old6, 6, 6, s.old))) return r;
     if (a2 && (r = download_cols(c, a2, 3, 3, s.a2))) return r;
     if (a3 && (r = download_cols(c, a3, 3, 3, s.a3))) return r;
-    if (p7 && (r = download_cols(c, p7, 7, 7, pc))) return r;
+    if (p7)
+    {
+        k_pack_pred<<<cdiv(c->n, 256), 256, 0, c->st>>>(c->d_stage, s, c->n);
+        LAUNCHED(c);
+        CU(cudaMemcpyAsync(p7, c->d_stage, (size_t)c->n * 7 * sizeof(double), cudaMemcpyDeviceToHost, c->st));
+        CU(cudaStreamSynchronize(c->st));
+    }
     if (t) CU(cudaMemcpyAsync(t, s.t, (size_t)c->n * sizeof(double), cudaMemcpyDeviceToHost, c->st));
     if (dt) CU(cudaMemcpyAsync(dt, s.dt, (size_t)c->n * sizeof(double), cudaMemcpyDeviceToHost, c->st));
     if (move) CU(cudaMemcpyAsync(move, s.move, (size_t)c->n * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->st));
@@ -419,48 +448,62 @@ struct ForcePlan
     uint32_t jb, je, per_split, nsplit, ld;
 };
 
-// Which kernel for how many active particles.  Large blocks: i in registers, j through the TMA ring,
-// biggest i-tile that still leaves every SM busy.  Small blocks: j across lanes (k_force_lane).  The
-// j-split is chosen so that (i-tiles x j-splits) covers the machine a few times over.
+// Which kernel for how many active particles (set from tools/sweep_force.py on a B200, see
+// profiles/): small blocks put j across lanes and read it straight from L2; from a few hundred active
+// particles on, i sits in registers and j streams through the per-warp TMA rings, with the biggest
+// i-tile that still leaves every SM busy.
 int pick_variant(const gdy_ctx *c, uint32_t nact)
 {
     if (c->tune_variant >= 0 && c->tune_variant < FV_COUNT) return c->tune_variant;
-    if (nact <= 1) return FV_LANE_I1;
-    if (nact <= 2) return FV_LANE_I2;
-    if (nact <= 4) return FV_LANE_I4;
-    if (nact <= 8) return FV_LANE_I8;
-    if (nact <= 16) return FV_LANE_I16;
-    if (nact <= 32) return FV_TILE_I32;
-    if (nact <= 64) return FV_TILE_I64;
-    const uint32_t full = (uint32_t)c->num_sms * 4;   // CTAs of 128 threads that fill the machine
-    if (nact >= 256 * full) return FV_TILE_I256;
-    if (nact % 256 > 0 && nact % 256 <= 128 && nact < 4096) return FV_TILE_I128;
-    return nact >= 1024 ? FV_TILE_I256 : FV_TILE_I128;
+    if (nact <= 2) return FV_LANE_I1x2;
+    const uint64_t nj = (uint64_t)(c->blk_end - c->blk_begin) * JB;
+    // j across lanes straight from L2 has the lower fixed cost (no pipeline fill, no second launch);
+    // it wins while the whole evaluation is a few tens of microseconds
+    if (nact <= 160 || (uint64_t)nact * nj <= 12000000ull) return FV_LANE_I1x4;
+    if (nact <= 8192) return FV_WARP_I64;
+    return FV_WARP_I256;
 }
 
+// j-split: CTAs = i-tiles x splits run in waves of (SMs x resident CTAs); the cost of a plan is
+// waves x (j-units per CTA + a fixed per-CTA overhead).  Minimising it fills the machine for small
+// blocks and avoids a ragged last wave for big ones.
 ForcePlan plan_force(const gdy_ctx *c, uint32_t nact)
 {
     ForcePlan p{};
     p.variant = pick_variant(c, nact);
     const ForceVariant &v = g_variants[p.variant];
     const uint32_t gx = cdiv(nact, (uint32_t)v.ti);
-    const uint32_t target = (uint32_t)c->num_sms * (v.threads >= 256 ? 3u : 6u);
+    const uint32_t slots = (uint32_t)c->num_sms * (uint32_t)(c->occ[p.variant] > 0 ? c->occ[p.variant] : 1);
     p.ld = round_up(nact, 32);
-    uint32_t units;   // j work items that can be split: tiles (tile kernels) or trips (lane kernels)
+    uint32_t units;   // j work items that can be split: blocks of 64 (warp kernels) or trips (lane kernels)
     if (v.kind == 0)
     {
-        p.jb = c->tile_begin; p.je = c->tile_end;
+        p.jb = c->blk_begin; p.je = c->blk_end;
         units = p.je - p.jb;
     }
     else
     {
-        p.jb = c->tile_begin * TJ;
-        p.je = c->tile_end * TJ < c->n ? c->tile_end * TJ : c->n;
+        p.jb = c->blk_begin * JB;
+        p.je = c->blk_end * JB < c->n ? c->blk_end * JB : c->n;
         if (p.je < p.jb) p.je = p.jb;
         units = cdiv(p.je - p.jb, (uint32_t)v.pj);
     }
-    uint32_t split = gx >= target ? 1u : cdiv(target, gx);
+    uint32_t split = 1;
     if (c->tune_jsplit > 0) split = (uint32_t)c->tune_jsplit;
+    else if (units > 1)
+    {
+        const uint64_t overhead = v.kind == 0 ? 3 : 2;   // per-CTA fixed cost in j-units
+        uint32_t smax = (8 * slots) / gx + 1;
+        if (smax > units) smax = units;
+        if (smax > 2048) smax = 2048;
+        uint64_t best = ~0ull;
+        for (uint32_t sp = 1; sp <= smax; ++sp)
+        {
+            const uint64_t waves = cdiv(gx * sp, slots);
+            const uint64_t cost = waves * (cdiv(units, sp) + overhead);
+            if (cost < best) { best = cost; split = sp; }
+        }
+    }
     const size_t max_split = c->part_cap / ((size_t)6 * p.ld);
     if (split > max_split) split = (uint32_t)max_split;
     if (split > units) split = units;
@@ -473,36 +516,37 @@ ForcePlan plan_force(const gdy_ctx *c, uint32_t nact)
     return p;
 }
 
-// Partial forces of `nact` i-particles (k-indexed views iv) against this shard's j-particles, summed
-// over the j-splits and over the shards.  *out = k-indexed [6][ld] buffer holding the result.
-int force_eval(gdy_ctx *c, uint32_t nact, IView iv, const double **out, uint32_t *ld_out, bool timed)
+// Partial forces of `nact` i-particles (move == NULL: particles 0..nact-1) against this shard's
+// j-particles, summed over the j-splits and over the shards.  *out = k-indexed [6][ld] result buffer.
+int force_eval(gdy_ctx *c, uint32_t nact, const uint32_t *move, const double **out, uint32_t *ld_out, bool timed)
 {
     const State &s = c->s;
     const ForcePlan p = plan_force(c, nact);
-    JView jv{s.p[0], s.p[1], s.p[2], s.p[3], s.p[4], s.p[5], s.m};
+    const ForceVariant &v = g_variants[p.variant];
+    ForceArgs a{};
+    a.pb = s.pb; a.move = move; a.part = s.part; a.fsum = s.fsum; a.counter = s.tile_counter;
+    a.nact = nact; a.ld = p.ld; a.jb = p.jb; a.je = p.je; a.per_split = p.per_split; a.e2 = c->e2;
     if (timed) CU(cudaEventRecord(c->ev0, c->st));
-    cudaError_t e = c->mask_self
-        ? launch_force<true>(p.variant, p.grid, c->st, jv, iv, s.part, nact, p.ld, p.jb, p.je, p.per_split, c->e2)
-        : launch_force<false>(p.variant, p.grid, c->st, jv, iv, s.part, nact, p.ld, p.jb, p.je, p.per_split, c->e2);
+    v.fn[c->mask_self ? 1 : 0]<<<p.grid, v.threads, v.smem, c->st>>>(a);
     ++c->launches;
-    if (e != cudaSuccess) return fail(c, GDY_ERR_CUDA, "force kernel %s grid (%u,%u): %s", g_variants[p.variant].name, p.grid.x, p.grid.y, cudaGetErrorString(e));
-    double *buf = s.part;
-    if (p.nsplit > 1)
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(c, GDY_ERR_CUDA, "force kernel %s grid (%u,%u): %s", v.name, p.grid.x, p.grid.y, cudaGetErrorString(e));
+    double *buf;
+    if (v.kind == 1) buf = s.fsum;            // lane kernels reduce their own j-splits
+    else if (p.nsplit > 1)
     {
         k_reduce_partials<<<cdiv(nact, 32), 256, 0, c->st>>>(s.part, s.fsum, nact, p.ld, p.nsplit);
         LAUNCHED(c);
         buf = s.fsum;
     }
+    else buf = s.part;
     if (timed) CU(cudaEventRecord(c->ev1, c->st));
-    if (c->world > 1)
+    if (c->world > 1 && c->comm)
         NC(g_nccl.AllReduce(buf, buf, (size_t)6 * p.ld, ncclDouble, ncclSum, c->comm, c->st));
     *out = buf;
     *ld_out = p.ld;
     return 0;
 }
-
-IView active_view(const State &s) { return IView{s.ip[0], s.ip[1], s.ip[2], s.ip[3], s.ip[4], s.ip[5]}; }
-IView identity_view(const State &s) { return IView{s.p[0], s.p[1], s.p[2], s.p[3], s.p[4], s.p[5]}; }
 
 int need_particles(gdy_ctx *c)
 {
@@ -532,7 +576,7 @@ extern "C" int gdy_init_acc_jrk(gdy_ctx *c)
     LAUNCHED(c);
     c->have_pred = true;
     const double *buf; uint32_t ld;
-    if ((r = force_eval(c, c->n, identity_view(s), &buf, &ld, false))) return r;
+    if ((r = force_eval(c, c->n, nullptr, &buf, &ld, false))) return r;
     k_scatter_forces<<<cdiv(c->n, 256), 256, 0, c->st>>>(s, nullptr, c->n, buf, ld);
     LAUNCHED(c);
     return GDY_OK;
@@ -592,14 +636,17 @@ int launch_min_time(gdy_ctx *c)
     return 0;
 }
 
-// predicted_pos_vel for this shard's j-slice (world == 1: everybody)
-int launch_predict(gdy_ctx *c, double itime)
+// predicted_pos_vel for this shard's j-slice (world == 1: everybody) plus `nextra` active particles
+int launch_predict(gdy_ctx *c, double itime, uint32_t nextra)
 {
-    uint32_t b = c->tile_begin * TJ, e = c->tile_end * TJ;
+    uint32_t b = c->blk_begin * JB, e = c->blk_end * JB;
     if (e > c->n) e = c->n;
-    if (e > b)
+    if (e < b) e = b;
+    if (c->world == 1) nextra = 0;   // the slice is everybody
+    const uint32_t cnt = (e - b) + nextra;
+    if (cnt)
     {
-        k_predict<<<cdiv(e - b, 256), 256, 0, c->st>>>(c->s, b, e, itime);
+        k_predict<<<cdiv(cnt, 256), 256, 0, c->st>>>(c->s, b, e, itime, c->s.move, nextra);
         LAUNCHED(c);
     }
     c->have_pred = true;
@@ -637,10 +684,9 @@ extern "C" int gdy_predicted_pos_vel(gdy_ctx *c, double itime)
     BIND(c);
     int r;
     if ((r = need_particles(c))) return r;
-    if (c->world == 1) return launch_predict(c, itime);
     // hook semantics = all N particles predicted on every shard (the fused driver predicts only the
     // shard's slice plus the active particles)
-    k_predict<<<cdiv(c->n, 256), 256, 0, c->st>>>(c->s, 0, c->n, itime);
+    k_predict<<<cdiv(c->n, 256), 256, 0, c->st>>>(c->s, 0, c->n, itime, nullptr, 0);
     LAUNCHED(c);
     c->have_pred = true;
     return GDY_OK;
@@ -654,11 +700,9 @@ extern "C" int gdy_update_acc_jrk(gdy_ctx *c, uint32_t nact)
     if (!c->have_pred) return fail(c, GDY_ERR_STATE, "update_acc_jrk before predicted_pos_vel/init_acc_jrk");
     if (nact == 0) return GDY_OK;
     State &s = c->s;
-    k_gather_active<<<cdiv(nact, 128), 128, 0, c->st>>>(s, s.move, nact, 0, 0, 0.0);
-    LAUNCHED(c);
     const double *buf; uint32_t ld;
     int r;
-    if ((r = force_eval(c, nact, active_view(s), &buf, &ld, false))) return r;
+    if ((r = force_eval(c, nact, s.move, &buf, &ld, false))) return r;
     k_scatter_forces<<<cdiv(nact, 128), 128, 0, c->st>>>(s, s.move, nact, buf, ld);
     LAUNCHED(c);
     return GDY_OK;
@@ -723,7 +767,8 @@ extern "C" int gdy_sync(gdy_ctx *c)
 // device and ONE host readback per block step ({next block time, next nact}, 16 bytes of pinned
 // memory): the scheduler of step k+1 is chained behind the corrector of step k.
 extern "C" int gdy_run(gdy_ctx *c, double atime, double itime0, double t_stop, uint64_t max_steps,
-                       gdy_run_stats *stats, uint32_t *trace_nact, double *trace_itime, uint64_t trace_cap)
+                       gdy_run_stats *stats, uint32_t *trace_nact, double *trace_itime, float *trace_us,
+                       uint64_t trace_cap)
 {
     if (!c) return GDY_ERR_INVALID;
     BIND(c);
@@ -741,6 +786,7 @@ extern "C" int gdy_run(gdy_ctx *c, double atime, double itime0, double t_stop, u
         if ((r = launch_sched(c, ATIME, false))) return r;
         CU(cudaStreamSynchronize(c->st));
     }
+    auto tick = std::chrono::steady_clock::now();
     while (ITIME < t_stop)
     {
         if (max_steps && it >= max_steps) break;
@@ -750,11 +796,9 @@ extern "C" int gdy_run(gdy_ctx *c, double atime, double itime0, double t_stop, u
         const bool last = !(ITIME < t_stop) || (max_steps && it + 1 >= max_steps);
         if (nact == 0) return fail(c, GDY_ERR_STATE, "no particle is due at block time %.17g", ITIME);
 
-        if ((r = launch_predict(c, ITIME))) return r;
-        k_gather_active<<<cdiv(nact, 128), 128, 0, c->st>>>(s, s.move, nact, 1, c->world > 1 ? 1 : 0, ITIME);
-        LAUNCHED(c);
+        if ((r = launch_predict(c, ITIME, nact))) return r;
         const double *buf; uint32_t ld;
-        if ((r = force_eval(c, nact, active_view(s), &buf, &ld, timed))) return r;
+        if ((r = force_eval(c, nact, s.move, &buf, &ld, timed))) return r;
         k_correct<<<cdiv(nact, 128), 128, 0, c->st>>>(s, nact, ITIME, (double)c->eta, buf, ld);
         LAUNCHED(c);
         if ((r = launch_min_time(c))) return r;
@@ -776,6 +820,12 @@ extern "C" int gdy_run(gdy_ctx *c, double atime, double itime0, double t_stop, u
         {
             if (trace_nact) trace_nact[it] = nact;
             if (trace_itime) trace_itime[it] = ITIME;
+            if (trace_us)
+            {
+                const auto now = std::chrono::steady_clock::now();
+                trace_us[it] = std::chrono::duration<float, std::micro>(now - tick).count();
+                tick = now;
+            }
         }
         inter += (uint64_t)nact * (uint64_t)c->n;
         nsteps += nact;
@@ -799,13 +849,10 @@ extern "C" int gdy_force_sweep(gdy_ctx *c, uint32_t nact, const uint32_t *move, 
     if (!c->have_pred) return fail(c, GDY_ERR_STATE, "force_sweep before predicted_pos_vel/init_acc_jrk");
     for (uint32_t k = 0; k < nact; ++k)
         if (move[k] >= c->n) return fail(c, GDY_ERR_INVALID, "move[%u] = %u out of range", k, move[k]);
-    State &s = c->s;
     CU(cudaMemcpyAsync(c->d_ilist, move, (size_t)nact * sizeof(uint32_t), cudaMemcpyHostToDevice, c->st));
-    k_gather_active<<<cdiv(nact, 128), 128, 0, c->st>>>(s, c->d_ilist, nact, 0, 0, 0.0);
-    LAUNCHED(c);
     const double *buf; uint32_t ld;
     int r;
-    if ((r = force_eval(c, nact, active_view(s), &buf, &ld, true))) return r;
+    if ((r = force_eval(c, nact, c->d_ilist, &buf, &ld, true))) return r;
     if (f6_out)
     {
         std::vector<double> tmp((size_t)6 * ld);
@@ -831,7 +878,7 @@ extern "C" int gdy_force_sweep_full(gdy_ctx *c, int reps, float *ms_out)
     const double *buf; uint32_t ld;
     for (int i = 0; i < reps; ++i)
     {
-        int r = force_eval(c, c->n, identity_view(c->s), &buf, &ld, false);
+        int r = force_eval(c, c->n, nullptr, &buf, &ld, false);
         if (r) return r;
     }
     CU(cudaEventRecord(b, c->st));
@@ -848,31 +895,33 @@ extern "C" int gdy_measure_fp64_peak(gdy_ctx *c, double *tflops_out, double *sm_
 {
     if (!c) return GDY_ERR_INVALID;
     BIND(c);
-    const int blocks = c->num_sms * 4, iters = 4096;   // one resident wave: 1024 threads per SM
-    double *out = c->s.part;                           // scratch
-    long long *cyc;
-    CU(cudaMalloc(&cyc, sizeof(long long)));
-    float best = 1e30f;
-    long long cycles = 0;
-    for (int rep = 0; rep < 6; ++rep)
-    {
-        CU(cudaEventRecord(c->ev0, c->st));
-        k_dfma_peak<<<blocks, 256, 0, c->st>>>(out, iters, 1.0000001, 1e-9, cyc);
-        LAUNCHED(c);
-        CU(cudaEventRecord(c->ev1, c->st));
-        CU(cudaStreamSynchronize(c->st));
-        float ms;
-        CU(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
-        if (rep >= 2 && ms < best)
+    const int iters = 4096;                            // x 64 DFMA per thread
+    double *out = c->s.part;                           // scratch (>= 8 Mi doubles)
+    using Fn = void (*)(double *, int, double, double);
+    const Fn fns[3] = {k_dfma_peak<4>, k_dfma_peak<8>, k_dfma_peak<16>};
+    double best_tf = 0.0;
+    for (int f = 0; f < 3; ++f)
+        for (int per_sm = 1; per_sm <= 8; per_sm *= 2)  // 256..2048 resident threads per SM
         {
-            best = ms;
-            CU(cudaMemcpy(&cycles, cyc, sizeof cycles, cudaMemcpyDeviceToHost));
+            const int blocks = c->num_sms * per_sm;
+            float best = 1e30f;
+            for (int rep = 0; rep < 4; ++rep)
+            {
+                CU(cudaEventRecord(c->ev0, c->st));
+                fns[f]<<<blocks, 256, 0, c->st>>>(out, iters, 1.0000001, 1e-9);
+                LAUNCHED(c);
+                CU(cudaEventRecord(c->ev1, c->st));
+                CU(cudaStreamSynchronize(c->st));
+                float ms;
+                CU(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+                if (rep >= 1 && ms < best) best = ms;
+            }
+            const double tf = 2.0 * 64.0 * iters * 256.0 * blocks / (best * 1e-3) / 1e12;
+            if (tf > best_tf) best_tf = tf;
         }
-    }
-    cudaFree(cyc);
-    const double flop = 2.0 * 64.0 * iters * 256.0 * blocks;
-    if (tflops_out) *tflops_out = flop / (best * 1e-3) / 1e12;
-    if (sm_mhz_out) *sm_mhz_out = (double)cycles / (best * 1e-3) / 1e6;
+    if (tflops_out) *tflops_out = best_tf;
+    // the SM clock this rate corresponds to if the pipe retires 64 DFMA lanes per SM per cycle
+    if (sm_mhz_out) *sm_mhz_out = best_tf * 1e12 / (2.0 * 64.0 * c->num_sms) / 1e6;
     return GDY_OK;
 }
 

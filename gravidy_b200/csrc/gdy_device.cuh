@@ -7,16 +7,22 @@
 
 namespace gdy {
 
-// j-tile size staged per pipeline stage, and the padding granule of every particle array.
-constexpr int TJ = 128;          // particles per TMA-staged j-tile (7 arrays x 1 KiB per stage)
-constexpr int NSTAGE = 4;        // pipeline depth of the j-tile ring
+// Layout granules.
+constexpr int JB = 64;           // particles per block of the blocked predicted array (one TMA bulk copy)
+constexpr int JROWS = 7;         // rows of a block: x y z vx vy vz m
+constexpr int JBD = JROWS * JB;  // doubles per block (3584 B)
 constexpr int PAD = 256;         // arrays are padded to a multiple of this (zero-mass far particles)
 constexpr double PAD_POS = 1.0e10;  // where the padding particles sit (mass 0 => contribute exactly 0)
 
-// Device-resident particle state, structure-of-arrays, every array npad doubles.
+// Device-resident particle state.  Plain arrays are structure-of-arrays, npad doubles each.
 // Reference data contract: double4 h_r{x,y,z,m}, double4 h_v, Forces h_f/h_old, double3 h_a2/h_a3,
 // double h_t/h_dt, Predictor h_p (reference: src/include/NbodySystem.hpp:100-115,
 // src/include/common.hpp:213-231).  Mass is a float-representable double (Predictor.m is float).
+//
+// The predicted set (the reference's h_p / d_p, what every force evaluation streams) is kept BLOCKED:
+// block b holds particles [64b, 64b+64) as 7 rows of 64 doubles (x y z vx vy vz m), 3584 contiguous
+// bytes, so that one cp.async.bulk (TMA) brings a whole j-tile into shared memory, already in the
+// row layout the inner loop reads with broadcast LDS.128.
 struct State
 {
     double *x, *y, *z, *m;          // h_r
@@ -25,15 +31,18 @@ struct State
     double *old[6];                 // h_old
     double *a2[3], *a3[3];          // h_a2, h_a3
     double *t, *dt;                 // h_t, h_dt
-    double *p[6];                   // h_p   : predicted x y z vx vy vz (mass shared with m)
+    double *pb;                     // h_p, blocked: [npad/64][7][64]
     uint32_t *move;                 // h_move
-    double *ip[6];                  // predicted pos/vel of the active list, gathered (k-indexed)
-    double *fsum;                   // [6][nact_pad] summed partial forces of the active list
-    double *part;                   // [S][6][nact_pad] j-split partial forces
+    double *fsum;                   // [6][ld] summed partial forces of the active list (k-indexed)
+    double *part;                   // [S][6][ld] j-split partial forces
+    uint32_t *tile_counter;         // arrival counters of the fused last-block reduction
 };
 
-struct JView { const double *x, *y, *z, *vx, *vy, *vz, *m; };
-struct IView { const double *x, *y, *z, *vx, *vy, *vz; };
+// index of row c of particle i in the blocked predicted array
+__host__ __device__ __forceinline__ size_t pbidx(uint32_t i, int c)
+{
+    return (size_t)(i >> 6) * JBD + (size_t)c * JB + (i & 63);
+}
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p)
 {
@@ -81,6 +90,13 @@ __device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src_gmem, u
             "r"(smem_u32(dst_smem)),
         "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
         : "memory");
+}
+
+// order this thread's (and, after a __syncwarp, its warp's) generic-proxy shared-memory reads before a
+// following async-proxy (TMA) write to the same buffer
+__device__ __forceinline__ void fence_proxy_async_smem()
+{
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 }
 
 // ---- FP64 reciprocal square root -------------------------------------------------------------

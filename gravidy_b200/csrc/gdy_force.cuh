@@ -1,198 +1,229 @@
 // gdy_force.cuh — the force kernels: FP64 acc+jerk of the active i-particles from a j-range.
 //
-// Replaces k_init_acc_jrk, k_update and (together with k_reduce_partials in gdy_step.cuh) k_reduce
-// (reference: src/include/gpu/Hermite4GPU_kernels.cu:47-87, 165-219, 226-248).  The reference uses
-// 32-thread CTAs, an AoS j-tile of 32 in shared memory, a fixed 16-way j-split and one thread per i
-// whatever nact is.  Here:
+// Replaces k_init_acc_jrk, k_update and k_reduce (reference: src/include/gpu/Hermite4GPU_kernels.cu:
+// 47-87, 165-219, 226-248).  The reference uses 32-thread CTAs, an AoS j-tile of 32 in shared memory, a
+// fixed 16-way j-split and one thread per i whatever nact is.  Here:
 //
-//   k_force_tile  (nact > 16): i-particles in registers (IPT per thread), 32 i per warp; j-tiles of
-//       TJ=128 particles x 7 SoA arrays are staged into a 4-deep shared-memory ring by 1-D TMA bulk
-//       copies (cp.async.bulk + mbarrier complete_tx) issued by one elected thread; every lane reads
-//       the same j (broadcast LDS.128 = two j per load).  WJ > 1 lets the warps of a CTA share one
-//       32-wide i-tile and split the j-tile, then sum through shared memory.
-//   k_force_lane  (nact <= 16): the warp is IL i-lanes x JL = 32/IL j-lanes; every j-lane streams its
-//       own j-particles straight from global/L2 (coalesced, no staging: each j is used IL*IPT times
-//       only), accumulators are folded over the j-lanes with xor-shuffles and over the warps through
-//       shared memory.  This is the "small active block" path: a block step with nact = 2 still
-//       spreads N j-particles over every SM.
+//   k_force_warp  (large and medium blocks): i-particles in registers (IPT per lane, 32 lanes), j-tiles
+//       of 64 particles = one 3584-byte block of the blocked predicted array, brought into a PER-WARP
+//       shared-memory ring by one cp.async.bulk (TMA, SASS UBLKCP) per tile with mbarrier complete_tx;
+//       every lane reads the same j (broadcast LDS.128 = two j per load).  Warps never wait for each
+//       other inside the j-loop (no CTA barrier per tile): a warp is a self-contained pipeline.  The
+//       warps of a CTA are arranged WI x WJ: WI different i-groups, WJ interleaved j-subranges of the
+//       same i-group, folded through shared memory at the end.
+//   k_force_lane  (small blocks): the warp is IL i-lanes x JL = 32/IL j-lanes; every j-lane streams its
+//       own j-particles straight from L2 (coalesced, no staging: each j is used IL*IPT times only),
+//       accumulators are folded over the j-lanes with xor-shuffles and over the warps through shared
+//       memory.  A block step with nact = 2 still spreads the N j-particles over every SM.  The j-split
+//       partials are summed by the LAST CTA to finish (arrival counter), in fixed split order, inside
+//       the same launch.
 //
-// Both write j-split partial sums part[split][6][nact_pad]; the split dimension is summed in a fixed
-// order afterwards (deterministic, so replicated multi-GPU state stays bit-identical).
+// Both write j-split partial sums part[split][6][ld]; the split dimension is always summed in a fixed
+// order (deterministic, so replicated multi-GPU state stays bit-identical).
 #pragma once
 #include "gdy_device.cuh"
 
 namespace gdy {
 
-// ------------------------------------------------------------------------------------------------------
-template <int IPT, int WI, int WJ, bool MASK>
-__global__ void __launch_bounds__(32 * WI * WJ)
-k_force_tile(JView jv, IView iv, double *__restrict__ part, uint32_t nact, uint32_t nact_pad,
-             uint32_t tile_begin, uint32_t tile_end, uint32_t tiles_per_split, double e2)
+// Arguments common to every force kernel (one struct: one signature, one launch table).
+struct ForceArgs
 {
-    constexpr int TI = 32 * WI * IPT;   // i-particles per CTA
-    constexpr int JW = TJ / WJ;         // j-particles of one tile handled by one warp
-    static_assert(TJ % (2 * WJ) == 0, "tile must split into j pairs per warp");
+    const double *pb;          // blocked predicted j-particles (and the i-particles, gathered by index)
+    const uint32_t *move;      // active list (k -> particle index); NULL = identity (full-active sweep)
+    double *part;              // [nsplit][6][ld]
+    double *fsum;              // [6][ld]   (lane kernels: written by the last CTA)
+    uint32_t *counter;         // [grid.x]  (lane kernels: arrival counters, left at 0)
+    uint32_t nact, ld;
+    uint32_t jb, je;           // j-range of this shard: blocks of 64 (warp kernels) / particles (lane kernels)
+    uint32_t per_split;        // same unit
+    double e2;
+};
 
-    __shared__ __align__(128) double sj[NSTAGE][7][TJ];
-    __shared__ __align__(8) uint64_t full[NSTAGE];
+struct IReg { double x, y, z, vx, vy, vz; };
+
+__device__ __forceinline__ IReg load_i(const ForceArgs &a, uint32_t k)
+{
+    const uint32_t kc = k < a.nact ? k : a.nact - 1;   // lanes past nact compute a duplicate, never stored
+    const uint32_t i = a.move ? a.move[kc] : kc;
+    const double *p = a.pb + pbidx(i, 0);
+    return IReg{p[0], p[JB], p[2 * JB], p[3 * JB], p[4 * JB], p[5 * JB]};
+}
+
+// ------------------------------------------------------------------------------------------------------
+template <int IPT, int WI, int WJ, int NST, bool MASK>
+__global__ void __launch_bounds__(32 * WI * WJ)
+k_force_warp(const ForceArgs a)
+{
+    constexpr int NW = WI * WJ;
+    constexpr int TI = 32 * WI * IPT;   // i-particles per CTA
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    double *ring = reinterpret_cast<double *>(smem_raw);                          // [NW][NST][JBD]
+    uint64_t *full = reinterpret_cast<uint64_t *>(ring + (size_t)NW * NST * JBD);  // [NW][NST]
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int wi = warp % WI, wj = warp / WI;
+    double *myring = ring + (size_t)warp * NST * JBD;
+    uint64_t *myfull = full + warp * NST;
 
-    const uint32_t tb = tile_begin + blockIdx.y * tiles_per_split;
-    const uint32_t te = min(tb + tiles_per_split, tile_end);
-    const int ntile = te > tb ? (int)(te - tb) : 0;
+    // this CTA's j-blocks, then this warp's (interleaved over the WJ j-warps)
+    const uint32_t b0 = a.jb + blockIdx.y * a.per_split;
+    const uint32_t b1 = min(b0 + a.per_split, a.je);
+    const int nb_cta = b1 > b0 ? (int)(b1 - b0) : 0;
+    const int nt = nb_cta > wj ? (nb_cta - wj + WJ - 1) / WJ : 0;   // tiles of this warp
 
-    if (tid == 0)
+    if (lane == 0)
     {
 #pragma unroll
-        for (int s = 0; s < NSTAGE; ++s) mbar_init(&full[s], 1);
+        for (int s = 0; s < NST; ++s) mbar_init(&myfull[s], 1);
         mbar_fence_init();
     }
     __syncthreads();
 
     auto issue = [&](int t) {
-        const int s = t % NSTAGE;
-        const size_t off = (size_t)(tb + t) * TJ;
-        mbar_expect_tx(&full[s], 7 * TJ * sizeof(double));
-        bulk_g2s(&sj[s][0][0], jv.x + off, TJ * sizeof(double), &full[s]);
-        bulk_g2s(&sj[s][1][0], jv.y + off, TJ * sizeof(double), &full[s]);
-        bulk_g2s(&sj[s][2][0], jv.z + off, TJ * sizeof(double), &full[s]);
-        bulk_g2s(&sj[s][3][0], jv.vx + off, TJ * sizeof(double), &full[s]);
-        bulk_g2s(&sj[s][4][0], jv.vy + off, TJ * sizeof(double), &full[s]);
-        bulk_g2s(&sj[s][5][0], jv.vz + off, TJ * sizeof(double), &full[s]);
-        bulk_g2s(&sj[s][6][0], jv.m + off, TJ * sizeof(double), &full[s]);
+        const int s = t % NST;
+        const double *src = a.pb + (size_t)(b0 + wj + (uint32_t)t * WJ) * JBD;
+        mbar_expect_tx(&myfull[s], JBD * sizeof(double));
+        bulk_g2s(myring + (size_t)s * JBD, src, JBD * sizeof(double), &myfull[s]);
     };
-    if (tid == 0)
+    if (lane == 0)
     {
-        const int pre = ntile < NSTAGE ? ntile : NSTAGE;
+        const int pre = nt < NST ? nt : NST;
         for (int t = 0; t < pre; ++t) issue(t);
     }
 
-    // i-particles of this thread (indices past nact are clamped; their results are never stored)
     uint32_t k[IPT];
-    double xi[IPT], yi[IPT], zi[IPT], vxi[IPT], vyi[IPT], vzi[IPT];
+    IReg ri[IPT];
     Acc6 acc[IPT];
 #pragma unroll
     for (int q = 0; q < IPT; ++q)
     {
-        k[q] = blockIdx.x * TI + q * (32 * WI) + wi * 32 + lane;
-        const uint32_t kc = k[q] < nact ? k[q] : nact - 1;
-        xi[q] = iv.x[kc]; yi[q] = iv.y[kc]; zi[q] = iv.z[kc];
-        vxi[q] = iv.vx[kc]; vyi[q] = iv.vy[kc]; vzi[q] = iv.vz[kc];
+        k[q] = blockIdx.x * TI + (wi * IPT + q) * 32 + lane;
+        ri[q] = load_i(a, k[q]);
         acc[q] = Acc6{0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
     }
+    const double e2 = a.e2;
 
-    for (int t = 0; t < ntile; ++t)
+    for (int t = 0; t < nt; ++t)
     {
-        const int s = t % NSTAGE;
-        mbar_wait(&full[s], (uint32_t)(t / NSTAGE) & 1u);
-        const double *bx = &sj[s][0][wj * JW], *by = &sj[s][1][wj * JW], *bz = &sj[s][2][wj * JW];
-        const double *bvx = &sj[s][3][wj * JW], *bvy = &sj[s][4][wj * JW], *bvz = &sj[s][5][wj * JW];
-        const double *bm = &sj[s][6][wj * JW];
+        const int s = t % NST;
+        mbar_wait(&myfull[s], (uint32_t)(t / NST) & 1u);
+        const double *b = myring + (size_t)s * JBD;
 #pragma unroll 2
-        for (int jj = 0; jj < JW; jj += 2)
+        for (int jj = 0; jj < JB; jj += 2)
         {
-            const double2 X = *reinterpret_cast<const double2 *>(bx + jj);
-            const double2 Y = *reinterpret_cast<const double2 *>(by + jj);
-            const double2 Z = *reinterpret_cast<const double2 *>(bz + jj);
-            const double2 VX = *reinterpret_cast<const double2 *>(bvx + jj);
-            const double2 VY = *reinterpret_cast<const double2 *>(bvy + jj);
-            const double2 VZ = *reinterpret_cast<const double2 *>(bvz + jj);
-            const double2 M = *reinterpret_cast<const double2 *>(bm + jj);
+            const double2 X = *reinterpret_cast<const double2 *>(b + 0 * JB + jj);
+            const double2 Y = *reinterpret_cast<const double2 *>(b + 1 * JB + jj);
+            const double2 Z = *reinterpret_cast<const double2 *>(b + 2 * JB + jj);
+            const double2 VX = *reinterpret_cast<const double2 *>(b + 3 * JB + jj);
+            const double2 VY = *reinterpret_cast<const double2 *>(b + 4 * JB + jj);
+            const double2 VZ = *reinterpret_cast<const double2 *>(b + 5 * JB + jj);
+            const double2 M = *reinterpret_cast<const double2 *>(b + 6 * JB + jj);
 #pragma unroll
             for (int q = 0; q < IPT; ++q)
-                pair<MASK>(acc[q], xi[q], yi[q], zi[q], vxi[q], vyi[q], vzi[q], X.x, Y.x, Z.x, VX.x,
-                           VY.x, VZ.x, M.x, e2);
+                pair<MASK>(acc[q], ri[q].x, ri[q].y, ri[q].z, ri[q].vx, ri[q].vy, ri[q].vz, X.x, Y.x, Z.x,
+                           VX.x, VY.x, VZ.x, M.x, e2);
 #pragma unroll
             for (int q = 0; q < IPT; ++q)
-                pair<MASK>(acc[q], xi[q], yi[q], zi[q], vxi[q], vyi[q], vzi[q], X.y, Y.y, Z.y, VX.y,
-                           VY.y, VZ.y, M.y, e2);
+                pair<MASK>(acc[q], ri[q].x, ri[q].y, ri[q].z, ri[q].vx, ri[q].vy, ri[q].vz, X.y, Y.y, Z.y,
+                           VX.y, VY.y, VZ.y, M.y, e2);
         }
-        __syncthreads();   // every warp is done with stage s -> it may be refilled
-        if (tid == 0 && t + NSTAGE < ntile) issue(t + NSTAGE);
+        __syncwarp();   // every lane is done with stage s -> it may be refilled
+        if (lane == 0 && t + NST < nt)
+        {
+            fence_proxy_async_smem();
+            issue(t + NST);
+        }
     }
 
-    double *out = part + (size_t)blockIdx.y * 6 * nact_pad;
+    double *out = a.part + (size_t)blockIdx.y * 6 * a.ld;
     if (WJ == 1)
     {
 #pragma unroll
         for (int q = 0; q < IPT; ++q)
-            if (k[q] < nact)
+            if (k[q] < a.nact)
             {
-                out[0 * (size_t)nact_pad + k[q]] = acc[q].ax;
-                out[1 * (size_t)nact_pad + k[q]] = acc[q].ay;
-                out[2 * (size_t)nact_pad + k[q]] = acc[q].az;
-                out[3 * (size_t)nact_pad + k[q]] = acc[q].jx;
-                out[4 * (size_t)nact_pad + k[q]] = acc[q].jy;
-                out[5 * (size_t)nact_pad + k[q]] = acc[q].jz;
+                out[0 * (size_t)a.ld + k[q]] = acc[q].ax;
+                out[1 * (size_t)a.ld + k[q]] = acc[q].ay;
+                out[2 * (size_t)a.ld + k[q]] = acc[q].az;
+                out[3 * (size_t)a.ld + k[q]] = acc[q].jx;
+                out[4 * (size_t)a.ld + k[q]] = acc[q].jy;
+                out[5 * (size_t)a.ld + k[q]] = acc[q].jz;
             }
     }
     else
     {
-        // fold the WJ j-warps: red[wj][q][c][wi*32+lane], aliased on the (now idle) tile ring
-        double *red = &sj[0][0][0];
-        static_assert(WJ * IPT * 6 * 32 * WI <= NSTAGE * 7 * TJ, "reduce buffer must fit the ring");
+        // fold the WJ j-warps in fixed order: red[wj][wi][q][c][lane], aliased on the (now idle) rings
+        static_assert((size_t)WJ * WI * IPT * 6 * 32 <= (size_t)NW * NST * JBD, "reduce buffer must fit the rings");
         __syncthreads();
+        double *red = ring;
 #pragma unroll
         for (int q = 0; q < IPT; ++q)
         {
-            double *r = red + ((size_t)(wj * IPT + q) * 6) * (32 * WI) + wi * 32 + lane;
-            r[0 * 32 * WI] = acc[q].ax; r[1 * 32 * WI] = acc[q].ay; r[2 * 32 * WI] = acc[q].az;
-            r[3 * 32 * WI] = acc[q].jx; r[4 * 32 * WI] = acc[q].jy; r[5 * 32 * WI] = acc[q].jz;
+            double *r = red + ((size_t)((wj * WI + wi) * IPT + q) * 6) * 32 + lane;
+            r[0 * 32] = acc[q].ax; r[1 * 32] = acc[q].ay; r[2 * 32] = acc[q].az;
+            r[3 * 32] = acc[q].jx; r[4 * 32] = acc[q].jy; r[5 * 32] = acc[q].jz;
         }
         __syncthreads();
         if (wj == 0)
         {
 #pragma unroll
             for (int q = 0; q < IPT; ++q)
-                if (k[q] < nact)
+                if (k[q] < a.nact)
                 {
 #pragma unroll
                     for (int c = 0; c < 6; ++c)
                     {
-                        double s = 0.0;
+                        double sum = 0.0;
 #pragma unroll
                         for (int w = 0; w < WJ; ++w)
-                            s += red[((size_t)(w * IPT + q) * 6 + c) * (32 * WI) + wi * 32 + lane];
-                        out[c * (size_t)nact_pad + k[q]] = s;
+                            sum += red[((size_t)((w * WI + wi) * IPT + q) * 6 + c) * 32 + lane];
+                        out[c * (size_t)a.ld + k[q]] = sum;
                     }
                 }
         }
     }
 }
 
+template <int IPT, int WI, int WJ, int NST>
+constexpr size_t force_warp_smem()
+{
+    return (size_t)WI * WJ * NST * JBD * sizeof(double) + (size_t)WI * WJ * NST * sizeof(uint64_t);
+}
+
 // ------------------------------------------------------------------------------------------------------
 template <int IL, int IPT, int WJ, bool MASK>
 __global__ void __launch_bounds__(32 * WJ)
-k_force_lane(JView jv, IView iv, double *__restrict__ part, uint32_t nact, uint32_t nact_pad,
-             uint32_t jbeg, uint32_t jend, uint32_t j_per_split, double e2)
+k_force_lane(const ForceArgs a)
 {
     constexpr int JL = 32 / IL;       // j-lanes per warp
     constexpr int TI = IL * IPT;      // i-particles per CTA
     constexpr int PJ = JL * WJ;       // j-particles in flight per CTA step
     constexpr int U = 4;              // independent j per lane per trip (memory-level parallelism)
+    constexpr int NT = 32 * WJ;       // threads
+    constexpr int NO = IPT * 6 * IL;  // outputs of this CTA
+    constexpr int G = NT / NO > 0 ? NT / NO : 1;   // split-groups of the final reduction
 
     __shared__ double red[WJ][IPT][6][IL];
+    __shared__ double red2[G][NO];
+    __shared__ uint32_t s_last;
 
     const int tid = threadIdx.x, lane = tid & 31, wj = tid >> 5;
     const int il = lane % IL, jl = lane / IL;
 
-    const uint32_t jb = jbeg + blockIdx.y * j_per_split;
-    const uint32_t je = min(jb + j_per_split, jend);
+    const uint32_t jb = a.jb + blockIdx.y * a.per_split;
+    const uint32_t je = min(jb + a.per_split, a.je);
 
     uint32_t k[IPT];
-    double xi[IPT], yi[IPT], zi[IPT], vxi[IPT], vyi[IPT], vzi[IPT];
+    IReg ri[IPT];
     Acc6 acc[IPT];
 #pragma unroll
     for (int q = 0; q < IPT; ++q)
     {
         k[q] = blockIdx.x * TI + q * IL + il;
-        const uint32_t kc = k[q] < nact ? k[q] : nact - 1;
-        xi[q] = iv.x[kc]; yi[q] = iv.y[kc]; zi[q] = iv.z[kc];
-        vxi[q] = iv.vx[kc]; vyi[q] = iv.vy[kc]; vzi[q] = iv.vz[kc];
+        ri[q] = load_i(a, k[q]);
         acc[q] = Acc6{0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
     }
+    const double e2 = a.e2;
 
     for (uint32_t base = jb; base < je; base += PJ * U)
     {
@@ -202,18 +233,18 @@ k_force_lane(JView jv, IView iv, double *__restrict__ part, uint32_t nact, uint3
         {
             const uint32_t j = base + (u * WJ + wj) * JL + jl;
             const bool ok = j < je;
-            const uint32_t jc = ok ? j : jb;
-            xj[u] = __ldg(jv.x + jc); yj[u] = __ldg(jv.y + jc); zj[u] = __ldg(jv.z + jc);
-            vxj[u] = __ldg(jv.vx + jc); vyj[u] = __ldg(jv.vy + jc); vzj[u] = __ldg(jv.vz + jc);
-            const double mm = __ldg(jv.m + jc);
+            const double *p = a.pb + pbidx(ok ? j : jb, 0);
+            xj[u] = __ldg(p); yj[u] = __ldg(p + JB); zj[u] = __ldg(p + 2 * JB);
+            vxj[u] = __ldg(p + 3 * JB); vyj[u] = __ldg(p + 4 * JB); vzj[u] = __ldg(p + 5 * JB);
+            const double mm = __ldg(p + 6 * JB);
             mj[u] = ok ? mm : 0.0;
         }
 #pragma unroll
         for (int u = 0; u < U; ++u)
 #pragma unroll
             for (int q = 0; q < IPT; ++q)
-                pair<MASK>(acc[q], xi[q], yi[q], zi[q], vxi[q], vyi[q], vzi[q], xj[u], yj[u], zj[u],
-                           vxj[u], vyj[u], vzj[u], mj[u], e2);
+                pair<MASK>(acc[q], ri[q].x, ri[q].y, ri[q].z, ri[q].vx, ri[q].vy, ri[q].vz, xj[u], yj[u],
+                           zj[u], vxj[u], vyj[u], vzj[u], mj[u], e2);
     }
 
     // fold the JL j-lanes (lane = jl*IL + il): xor offsets IL, 2IL, ..., 16
@@ -237,39 +268,140 @@ k_force_lane(JView jv, IView iv, double *__restrict__ part, uint32_t nact, uint3
         }
     }
     __syncthreads();
-    // fold the WJ warps in fixed order; IPT*6*IL outputs per CTA
-    double *out = part + (size_t)blockIdx.y * 6 * nact_pad;
-    for (int o = tid; o < IPT * 6 * IL; o += 32 * WJ)
+    // fold the WJ warps in fixed order; NO outputs per CTA.  Output o = (q, c, l).
+    const uint32_t nsplit = gridDim.y;
+    double *out = (nsplit == 1 ? a.fsum : a.part + (size_t)blockIdx.y * 6 * a.ld);
+    for (int o = tid; o < NO; o += NT)
     {
         const int l = o % IL, c = (o / IL) % 6, q = o / (6 * IL);
         const uint32_t kk = blockIdx.x * TI + q * IL + l;
-        if (kk < nact)
+        if (kk < a.nact)
         {
             double s = 0.0;
 #pragma unroll
             for (int w = 0; w < WJ; ++w) s += red[w][q][c][l];
-            out[c * (size_t)nact_pad + kk] = s;
+            out[c * (size_t)a.ld + kk] = s;
         }
+    }
+    if (nsplit == 1) return;
+
+    // ---- fused j-split reduction: the last CTA of this i-tile to arrive sums all splits ------------------
+    __threadfence();
+    __syncthreads();
+    if (tid == 0)
+    {
+        const uint32_t prev = atomicAdd(&a.counter[blockIdx.x], 1u);
+        s_last = (prev == nsplit - 1) ? 1u : 0u;
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    // thread (g, o): splits g, g+G, ... in ascending order; then the G group sums in ascending g.
+    // The decomposition depends only on the launch shape, never on which CTA happens to be last.
+    for (int idx = tid; idx < G * NO; idx += NT)
+    {
+        const int o = idx % NO, g = idx / NO;
+        const int l = o % IL, c = (o / IL) % 6, q = o / (6 * IL);
+        const uint32_t kk = blockIdx.x * TI + q * IL + l;
+        double s = 0.0;
+        if (kk < a.nact)
+        {
+            const volatile double *p = a.part + c * (size_t)a.ld + kk;
+            const size_t stride = (size_t)6 * a.ld;
+            uint32_t sp = g;
+            for (; sp + 7 * G < nsplit; sp += 8 * G)
+            {
+                double v[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) v[u] = p[(size_t)(sp + u * G) * stride];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) s += v[u];
+            }
+            for (; sp < nsplit; sp += G) s += p[(size_t)sp * stride];
+        }
+        red2[g][o] = s;
+    }
+    __syncthreads();
+    for (int o = tid; o < NO; o += NT)
+    {
+        const int l = o % IL, c = (o / IL) % 6, q = o / (6 * IL);
+        const uint32_t kk = blockIdx.x * TI + q * IL + l;
+        if (kk < a.nact)
+        {
+            double s = 0.0;
+#pragma unroll
+            for (int g = 0; g < G; ++g) s += red2[g][o];
+            a.fsum[c * (size_t)a.ld + kk] = s;
+        }
+    }
+    if (tid == 0) a.counter[blockIdx.x] = 0;   // ready for the next launch (stream-ordered)
+}
+
+// Sum the j-split partials of the warp kernels in ascending split order (deterministic) -> fsum[6][ld].
+// Replaces k_reduce (reference: src/include/gpu/Hermite4GPU_kernels.cu:226-248).
+// Block = 32 k-lanes x 8 split-warps: coalesced over k, the splits strided over the warps (4 loads in
+// flight per thread) and folded through shared memory in warp order.
+__global__ void __launch_bounds__(256)
+k_reduce_partials(const double *__restrict__ part, double *__restrict__ fsum, uint32_t nact,
+                  uint32_t ld, uint32_t nsplit)
+{
+    __shared__ double red[8][6][32];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const uint32_t k = blockIdx.x * 32 + lane;
+    double acc[6] = {0, 0, 0, 0, 0, 0};
+    if (k < nact)
+    {
+        const size_t stride = (size_t)6 * ld;
+        uint32_t sp = w;
+        for (; sp + 24 < nsplit; sp += 32)
+        {
+            double v[4][6];
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+#pragma unroll
+                for (int c = 0; c < 6; ++c) v[u][c] = part[(size_t)(sp + 8 * u) * stride + (size_t)c * ld + k];
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+#pragma unroll
+                for (int c = 0; c < 6; ++c) acc[c] += v[u][c];
+        }
+        for (; sp < nsplit; sp += 8)
+#pragma unroll
+            for (int c = 0; c < 6; ++c) acc[c] += part[(size_t)sp * stride + (size_t)c * ld + k];
+    }
+#pragma unroll
+    for (int c = 0; c < 6; ++c) red[w][c][lane] = acc[c];
+    __syncthreads();
+    if (w < 6 && k < nact)
+    {
+        double sum = 0.0;
+#pragma unroll
+        for (int ww = 0; ww < 8; ++ww) sum += red[ww][w][lane];
+        fsum[(size_t)w * ld + k] = sum;
     }
 }
 
 // ------------------------------------------------------------------------------------------------------
-// Variant table.  kind 0 = tile (j staged through shared memory), 1 = lane (j from global).
+// Variant table.  kind 0 = warp kernel (j staged through shared memory by TMA), 1 = lane (j from L2).
+using ForceFn = void (*)(const ForceArgs);
+
 struct ForceVariant
 {
-    int kind;       // 0 tile, 1 lane
+    int kind;       // 0 warp, 1 lane
     int ti;         // i-particles per CTA
     int threads;    // CTA size
-    int pj;         // lane kernels: j-particles per CTA trip (PJ*U); tile kernels: TJ
+    int pj;         // lane kernels: j-particles per CTA trip (PJ*U); warp kernels: JB
+    size_t smem;    // dynamic shared memory
     const char *name;
+    ForceFn fn[2];  // [MASK]
 };
 
 enum : int
 {
-    FV_TILE_I256 = 0,   // IPT=2 WI=4 WJ=1
-    FV_TILE_I128,       // IPT=1 WI=4 WJ=1
-    FV_TILE_I64,        // IPT=2 WI=1 WJ=4
-    FV_TILE_I32,        // IPT=1 WI=1 WJ=4
+    FV_WARP_I256 = 0,   // IPT=2 WI=4 WJ=1
+    FV_WARP_I128,       // IPT=2 WI=2 WJ=2
+    FV_WARP_I64,        // IPT=2 WI=1 WJ=4
+    FV_WARP_I32,        // IPT=1 WI=1 WJ=4
     FV_LANE_I16,        // IL=16
     FV_LANE_I8,         // IL=8
     FV_LANE_I4,         // IL=4
@@ -277,40 +409,44 @@ enum : int
     FV_LANE_I1,         // IL=1
     FV_LANE_I1x2,       // IL=1 IPT=2
     FV_LANE_I1x4,       // IL=1 IPT=4
-    FV_TILE_I512,       // IPT=2 WI=8 WJ=1
+    FV_WARP_I512,       // IPT=2 WI=8 WJ=1
+    FV_WARP_I128H,      // IPT=1 WI=4 WJ=1 (high occupancy)
+    FV_LANE_I16x2,      // IL=16 IPT=2 (32 i per CTA)
+    FV_LANE_I16x4,      // IL=16 IPT=4 (64 i per CTA)
+    FV_LANE_I1x8,       // IL=1 IPT=8
     FV_COUNT
 };
 
+#define GDY_WARP(ipt, wi, wj, nst, nm) \
+    {0, 32 * (wi) * (ipt), 32 * (wi) * (wj), JB, force_warp_smem<ipt, wi, wj, nst>(), nm, \
+     {k_force_warp<ipt, wi, wj, nst, false>, k_force_warp<ipt, wi, wj, nst, true>}}
+#define GDY_LANE(il, ipt, nm) \
+    {1, (il) * (ipt), 128, (32 / (il)) * 4 * 4, 0, nm, \
+     {k_force_lane<il, ipt, 4, false>, k_force_lane<il, ipt, 4, true>}}
+
 static const ForceVariant g_variants[FV_COUNT] = {
-    {0, 256, 128, TJ, "tile_i256"}, {0, 128, 128, TJ, "tile_i128"}, {0, 64, 128, TJ, "tile_i64"},
-    {0, 32, 128, TJ, "tile_i32"},   {1, 16, 128, 2 * 4 * 4, "lane_i16"}, {1, 8, 128, 4 * 4 * 4, "lane_i8"},
-    {1, 4, 128, 8 * 4 * 4, "lane_i4"}, {1, 2, 128, 16 * 4 * 4, "lane_i2"}, {1, 1, 128, 32 * 4 * 4, "lane_i1"},
-    {1, 2, 128, 32 * 4 * 4, "lane_i1x2"}, {1, 4, 128, 32 * 4 * 4, "lane_i1x4"}, {0, 512, 256, TJ, "tile_i512"},
+    GDY_WARP(2, 4, 1, 3, "warp_i256"), GDY_WARP(2, 2, 2, 3, "warp_i128"), GDY_WARP(2, 1, 4, 3, "warp_i64"),
+    GDY_WARP(1, 1, 4, 2, "warp_i32"),
+    GDY_LANE(16, 1, "lane_i16"), GDY_LANE(8, 1, "lane_i8"), GDY_LANE(4, 1, "lane_i4"),
+    GDY_LANE(2, 1, "lane_i2"), GDY_LANE(1, 1, "lane_i1"), GDY_LANE(1, 2, "lane_i1x2"),
+    GDY_LANE(1, 4, "lane_i1x4"),
+    GDY_WARP(2, 8, 1, 3, "warp_i512"), GDY_WARP(1, 4, 1, 2, "warp_i128h"),
+    GDY_LANE(16, 2, "lane_i16x2"), GDY_LANE(16, 4, "lane_i16x4"), GDY_LANE(1, 8, "lane_i1x8"),
 };
 
-template <bool MASK>
-static cudaError_t launch_force(int variant, dim3 grid, cudaStream_t st, JView jv, IView iv,
-                                double *part, uint32_t nact, uint32_t nact_pad, uint32_t jb,
-                                uint32_t je, uint32_t per_split, double e2)
+// opt in to > 48 KiB of dynamic shared memory where a variant needs it (once per process and device)
+static cudaError_t force_variants_prepare()
 {
-    // tile kernels take tile units (jb, je, per_split in tiles of TJ); lane kernels take particles
-    switch (variant)
-    {
-    case FV_TILE_I256: k_force_tile<2, 4, 1, MASK><<<grid, 128, 0, st>>>(jv, iv, part, nact, nact_pad, jb, je, per_split, e2); break;
-    case FV_TILE_I128: k_force_tile<1, 4, 1, MASK><<<grid, 128, 0, st>>>(jv, iv, part, nact, nact_pad, jb, je, per_split, e2); break;
-    case FV_TILE_I64:  k_force_tile<2, 1, 4, MASK><<<grid, 128, 0, st>>>(jv, iv, part, nact, nact_pad, jb, je, per_split, e2); break;
-    case FV_TILE_I32:  k_force_tile<1, 1, 4, MASK><<<grid, 128, 0, st>>>(jv, iv, part, nact, nact_pad, jb, je, per_split, e2); break;
-    case FV_LANE_I16:  k_force_lane<16, 1, 4, MASK><<<grid, 128, 0, st>>>(jv, iv, part, nact, nact_pad, jb, je, per_split, e2); break;
-    case FV_LANE_I8:   k_force_lane<8, 1, 4, MASK><<<grid, 128, 0, st>>>(jv, iv, part, nact, nact_pad, jb, je, per_split, e2); break;
-    case FV_LANE_I4:   k_force_lane<4, 1, 4, MASK><<<grid, 128, 0, st>>>(jv, iv, part, nact, nact_pad, jb, je, per_split, e2); break;
-    case FV_LANE_I2:   k_force_lane<2, 1, 4, MASK><<<grid, 128, 0, st>>>(jv, iv, part, nact, nact_pad, jb, je, per_split, e2); break;
-    case FV_LANE_I1:   k_force_lane<1, 1, 4, MASK><<<grid, 128, 0, st>>>(jv, iv, part, nact, nact_pad, jb, je, per_split, e2); break;
-    case FV_LANE_I1x2: k_force_lane<1, 2, 4, MASK><<<grid, 128, 0, st>>>(jv, iv, part, nact, nact_pad, jb, je, per_split, e2); break;
-    case FV_LANE_I1x4: k_force_lane<1, 4, 4, MASK><<<grid, 128, 0, st>>>(jv, iv, part, nact, nact_pad, jb, je, per_split, e2); break;
-    case FV_TILE_I512: k_force_tile<2, 8, 1, MASK><<<grid, 256, 0, st>>>(jv, iv, part, nact, nact_pad, jb, je, per_split, e2); break;
-    default: return cudaErrorInvalidValue;
-    }
-    return cudaGetLastError();
+    for (int v = 0; v < FV_COUNT; ++v)
+        for (int m = 0; m < 2; ++m)
+            if (g_variants[v].smem > 48 * 1024)
+            {
+                cudaError_t e = cudaFuncSetAttribute((const void *)g_variants[v].fn[m],
+                                                     cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                     (int)g_variants[v].smem);
+                if (e != cudaSuccess) return e;
+            }
+    return cudaSuccess;
 }
 
 }  // namespace gdy

@@ -46,58 +46,53 @@ __device__ __forceinline__ Pred6 predict_one(const State &s, uint32_t i, double 
     return p;
 }
 
-// predicted_pos_vel(ITIME) for particles [begin, end).  Replaces k_prediction (reference:
-// src/include/gpu/Hermite4GPU_kernels.cu:127-158).
-__global__ void k_predict(State s, uint32_t begin, uint32_t end, double itime)
+__device__ __forceinline__ void store_pred(const State &s, uint32_t i, const Pred6 &p)
 {
-    const uint32_t i = begin + blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= end) return;
-    const Pred6 p = predict_one(s, i, itime);
-    s.p[0][i] = p.x; s.p[1][i] = p.y; s.p[2][i] = p.z;
-    s.p[3][i] = p.vx; s.p[4][i] = p.vy; s.p[5][i] = p.vz;
+    double *q = s.pb + pbidx(i, 0);
+    q[0] = p.x; q[JB] = p.y; q[2 * JB] = p.z;
+    q[3 * JB] = p.vx; q[4 * JB] = p.vy; q[5 * JB] = p.vz;
+}
+
+// predicted_pos_vel(ITIME) for particles [begin, end), written to the blocked predicted array.
+// Replaces k_prediction (reference: src/include/gpu/Hermite4GPU_kernels.cu:127-158).
+// nextra > 0: threads past the range predict the active particles move[0..nextra) as well — with the
+// j-particles sharded over GPUs a rank predicts only its own j-slice, but the force kernel reads the
+// predicted i-particles and the corrector needs p[i] of EVERY active particle.  Same arithmetic, so a
+// particle predicted twice gets the same bits twice.
+__global__ void k_predict(State s, uint32_t begin, uint32_t end, double itime,
+                          const uint32_t *__restrict__ move, uint32_t nextra)
+{
+    const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t i;
+    if (g < end - begin) i = begin + g;
+    else if (g - (end - begin) < nextra) i = move[g - (end - begin)];
+    else return;
+    store_pred(s, i, predict_one(s, i, itime));
 }
 
 // init: predicted = current (reference: Hermite4::init_data, src/include/Hermite4.cpp:198-210)
-__global__ void k_copy_to_pred(State s, uint32_t npad)
+__global__ void k_copy_to_pred(State s, uint32_t n)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    store_pred(s, i, Pred6{s.x[i], s.y[i], s.z[i], s.vx[i], s.vy[i], s.vz[i]});
+}
+
+// mass row (and, for the padding particles, the far-away position) of the blocked predicted array
+__global__ void k_init_pb(State s, uint32_t n, uint32_t npad)
 {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= npad) return;
-    s.p[0][i] = s.x[i]; s.p[1][i] = s.y[i]; s.p[2][i] = s.z[i];
-    s.p[3][i] = s.vx[i]; s.p[4][i] = s.vy[i]; s.p[5][i] = s.vz[i];
-}
-
-// Gather the predicted pos/vel of the active list into k-indexed arrays (the i-particles of the force
-// kernels; replaces the host gather + H2D copy of h_i, reference: src/include/gpu/Hermite4GPU.cu:405-421)
-// and, when save_old is set, do save_old_acc_jrk for them (reference: src/include/Hermite4.cpp:145-153).
-// do_predict: the prediction of the active particle is computed here (same arithmetic as k_predict, so
-// bit-identical) and stored to p[i] as well — with the j-particles sharded over GPUs a rank only
-// predicts its own j-slice in k_predict, but the corrector needs p[i] of every active particle.
-__global__ void k_gather_active(State s, const uint32_t *__restrict__ move, uint32_t nact,
-                                int save_old, int do_predict, double itime)
-{
-    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
-    if (k >= nact) return;
-    const uint32_t i = move[k];
-    if (do_predict)
-    {
-        const Pred6 p = predict_one(s, i, itime);
-        s.p[0][i] = p.x; s.p[1][i] = p.y; s.p[2][i] = p.z;
-        s.p[3][i] = p.vx; s.p[4][i] = p.vy; s.p[5][i] = p.vz;
-        s.ip[0][k] = p.x; s.ip[1][k] = p.y; s.ip[2][k] = p.z;
-        s.ip[3][k] = p.vx; s.ip[4][k] = p.vy; s.ip[5][k] = p.vz;
-    }
+    double *q = s.pb + pbidx(i, 0);
+    if (i < n) q[6 * JB] = s.m[i];
     else
     {
-#pragma unroll
-        for (int c = 0; c < 6; ++c) s.ip[c][k] = s.p[c][i];
-    }
-    if (save_old)
-    {
-#pragma unroll
-        for (int c = 0; c < 6; ++c) s.old[c][i] = s.f[c][i];
+        q[0] = PAD_POS; q[JB] = PAD_POS; q[2 * JB] = PAD_POS;
+        q[3 * JB] = 0.0; q[4 * JB] = 0.0; q[5 * JB] = 0.0; q[6 * JB] = 0.0;
     }
 }
 
+// save_old_acc_jrk(nact) (reference: src/include/Hermite4.cpp:145-153)
 __global__ void k_save_old(State s, uint32_t nact)
 {
     const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
@@ -105,37 +100,6 @@ __global__ void k_save_old(State s, uint32_t nact)
     const uint32_t i = s.move[k];
 #pragma unroll
     for (int c = 0; c < 6; ++c) s.old[c][i] = s.f[c][i];
-}
-
-// Sum the j-split partials in ascending split order (deterministic) -> fsum[6][nact_pad].
-// Replaces k_reduce (reference: src/include/gpu/Hermite4GPU_kernels.cu:226-248).
-// Block = 32 k-lanes x 8 split-warps: coalesced over k, the splits strided over the warps and
-// folded through shared memory in warp order.
-__global__ void __launch_bounds__(256)
-k_reduce_partials(const double *__restrict__ part, double *__restrict__ fsum, uint32_t nact,
-                  uint32_t nact_pad, uint32_t nsplit)
-{
-    __shared__ double red[8][6][32];
-    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    const uint32_t k = blockIdx.x * 32 + lane;
-    double a[6] = {0, 0, 0, 0, 0, 0};
-    if (k < nact)
-        for (uint32_t sp = w; sp < nsplit; sp += 8)
-        {
-            const double *p = part + (size_t)sp * 6 * nact_pad + k;
-#pragma unroll
-            for (int c = 0; c < 6; ++c) a[c] += p[(size_t)c * nact_pad];
-        }
-#pragma unroll
-    for (int c = 0; c < 6; ++c) red[w][c][lane] = a[c];
-    __syncthreads();
-    if (w < 6 && k < nact)
-    {
-        double sum = 0.0;
-#pragma unroll
-        for (int ww = 0; ww < 8; ++ww) sum += red[ww][w][lane];
-        fsum[(size_t)w * nact_pad + k] = sum;
-    }
 }
 
 // h_f[move[k]] = summed force (the tail of update_acc_jrk).  fbuf = [6][ld], k-indexed.
@@ -180,8 +144,10 @@ __device__ __forceinline__ double normalize_dt(double new_dt, double old_dt, dou
 // correction_pos_vel(ITIME, nact) with get_timestep_normal + normalize_dt.  Expression order of the
 // CPU back end (reference: src/include/cpu/Hermite4CPU.cpp:370-411, NbodyUtils.cpp:337-365).
 // The reference runs this on the host even in its GPU build (reference: Hermite4GPU.cu:274-328).
-// fbuf != NULL: the new forces are taken from the k-indexed buffer [6][ld] the force path produced and
-// stored to h_f here (fuses the scatter at the end of update_acc_jrk into the corrector).
+// fbuf != NULL (fused driver): the new forces are taken from the k-indexed buffer [6][ld] the force path
+// produced and stored to h_f here, and the forces they replace are saved to h_old on the way — the
+// scatter at the end of update_acc_jrk and save_old_acc_jrk (reference: src/include/Hermite4.cpp:145-153)
+// fused into the corrector; same values, two launches fewer.
 __global__ void k_correct(State s, uint32_t nact, double itime, double eta,
                           const double *__restrict__ fbuf, uint32_t ld)
 {
@@ -200,9 +166,11 @@ __global__ void k_correct(State s, uint32_t nact, double itime, double eta,
 #pragma unroll
     for (int c = 0; c < 3; ++c)
     {
-        const double oa = s.old[c][i], oj = s.old[3 + c][i];
+        double oa, oj;
         if (fbuf)
         {
+            oa = s.f[c][i]; oj = s.f[3 + c][i];
+            s.old[c][i] = oa; s.old[3 + c][i] = oj;
             fa[c] = fbuf[(size_t)c * ld + k];
             fj[c] = fbuf[(size_t)(3 + c) * ld + k];
             s.f[c][i] = fa[c];
@@ -210,6 +178,7 @@ __global__ void k_correct(State s, uint32_t nact, double itime, double eta,
         }
         else
         {
+            oa = s.old[c][i]; oj = s.old[3 + c][i];
             fa[c] = s.f[c][i];
             fj[c] = s.f[3 + c][i];
         }
@@ -222,12 +191,13 @@ __global__ void k_correct(State s, uint32_t nact, double itime, double eta,
         s.a3[c][i] = a3[c];
     }
     // r = p.r + (dt4/24)*a2 + (dt5/120)*a3 ;  v = p.v + (dt3/6)*a2 + (dt4/24)*a3
-    s.x[i] = add(add(s.p[0][i], mul(c4_24, a2[0])), mul(c5_120, a3[0]));
-    s.y[i] = add(add(s.p[1][i], mul(c4_24, a2[1])), mul(c5_120, a3[1]));
-    s.z[i] = add(add(s.p[2][i], mul(c4_24, a2[2])), mul(c5_120, a3[2]));
-    s.vx[i] = add(add(s.p[3][i], mul(c3_6, a2[0])), mul(c4_24, a3[0]));
-    s.vy[i] = add(add(s.p[4][i], mul(c3_6, a2[1])), mul(c4_24, a3[1]));
-    s.vz[i] = add(add(s.p[5][i], mul(c3_6, a2[2])), mul(c4_24, a3[2]));
+    const double *pp = s.pb + pbidx(i, 0);
+    s.x[i] = add(add(pp[0], mul(c4_24, a2[0])), mul(c5_120, a3[0]));
+    s.y[i] = add(add(pp[JB], mul(c4_24, a2[1])), mul(c5_120, a3[1]));
+    s.z[i] = add(add(pp[2 * JB], mul(c4_24, a2[2])), mul(c5_120, a3[2]));
+    s.vx[i] = add(add(pp[3 * JB], mul(c3_6, a2[0])), mul(c4_24, a3[0]));
+    s.vy[i] = add(add(pp[4 * JB], mul(c3_6, a2[1])), mul(c4_24, a3[1]));
+    s.vz[i] = add(add(pp[5 * JB], mul(c3_6, a2[2])), mul(c4_24, a3[2]));
     s.t[i] = itime;
 
     // get_timestep_normal(i, eta): h_dt[i] is still the old step here
@@ -472,6 +442,15 @@ __global__ void k_pack(double *__restrict__ aos, Cols cols, int ncol, int stride
     if (i >= n) return;
     for (int c = 0; c < ncol; ++c) aos[(size_t)i * stride + c] = cols.c[c] ? cols.c[c][i] : 0.0;
 }
+// Predictor h_p as AoS {r[3], v[3], m} from the blocked array (download only)
+__global__ void k_pack_pred(double *__restrict__ aos, State s, uint32_t n)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const double *q = s.pb + pbidx(i, 0);
+#pragma unroll
+    for (int c = 0; c < 7; ++c) aos[(size_t)i * 7 + c] = q[c * JB];
+}
 __global__ void k_fill(double *p, double v, uint32_t begin, uint32_t end)
 {
     const uint32_t i = begin + blockIdx.x * blockDim.x + threadIdx.x;
@@ -479,25 +458,26 @@ __global__ void k_fill(double *p, double v, uint32_t begin, uint32_t end)
 }
 
 // ---- measurement micro-kernels (roofline denominators; not on the hot path) -------------------------
-// 8 independent DFMA chains per thread: the FP64 pipe's issue rate, nothing else.
-__global__ void __launch_bounds__(256) k_dfma_peak(double *out, int iters, double a, double b,
-                                                    long long *cycles)
+// NCH independent DFMA chains per thread: the FP64 pipe's issue rate, nothing else.  The host tries a few
+// (chains, residency) shapes and keeps the best, so the denominator is the most the pipe has been seen
+// to sustain, not an artefact of one instruction schedule.
+template <int NCH>
+__global__ void __launch_bounds__(256) k_dfma_peak(double *out, int iters, double a, double b)
 {
-    double x0 = threadIdx.x, x1 = x0 + 1, x2 = x0 + 2, x3 = x0 + 3, x4 = x0 + 4, x5 = x0 + 5,
-           x6 = x0 + 6, x7 = x0 + 7;
-    const long long c0 = clock64();
+    double x[NCH];
+#pragma unroll
+    for (int c = 0; c < NCH; ++c) x[c] = (double)(threadIdx.x + c);
     for (int it = 0; it < iters; ++it)
     {
 #pragma unroll
-        for (int u = 0; u < 8; ++u)
-        {
-            x0 = fma(x0, a, b); x1 = fma(x1, a, b); x2 = fma(x2, a, b); x3 = fma(x3, a, b);
-            x4 = fma(x4, a, b); x5 = fma(x5, a, b); x6 = fma(x6, a, b); x7 = fma(x7, a, b);
-        }
+        for (int u = 0; u < 64 / NCH; ++u)
+#pragma unroll
+            for (int c = 0; c < NCH; ++c) x[c] = fma(x[c], a, b);
     }
-    const long long c1 = clock64();
-    out[blockIdx.x * blockDim.x + threadIdx.x] = ((x0 + x1) + (x2 + x3)) + ((x4 + x5) + (x6 + x7));
-    if (blockIdx.x == 0 && threadIdx.x == 0) *cycles = c1 - c0;
+    double s = 0.0;
+#pragma unroll
+    for (int c = 0; c < NCH; ++c) s += x[c];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
 }
 
 }  // namespace gdy

@@ -42,7 +42,7 @@ class Hermite4B200:
         self.eta = np.float32(eta)
         self.h = capi._ctx()
         uid = None
-        if world > 1:
+        if world > 1 and nccl_uid is not None:
             uid = (C.c_uint8 * capi.NCCL_UID_BYTES).from_buffer_copy(bytes(nccl_uid))
         rc = self.lib.gdy_create_sharded(C.byref(self.h), self.n, self.e2, C.c_float(float(self.eta)),
                                          device, rank, world, uid)
@@ -78,6 +78,15 @@ class Hermite4B200:
         if rc:
             raise capi.GdyError(rc, lib.gdy_last_error(None).decode())
         return bytes(buf)
+
+    @staticmethod
+    def shard_range(n, rank, world):
+        """[begin, end) of the j-particles shard `rank` of `world` computes (host arithmetic only)."""
+        b, e = C.c_uint32(), C.c_uint32()
+        rc = capi.load().gdy_shard_range(n, rank, world, C.byref(b), C.byref(e))
+        if rc:
+            raise capi.GdyError(rc, "bad shard arguments")
+        return b.value, e.value
 
     # ---- transfers -----------------------------------------------------------------------------
     def upload_particles(self, r4, v4):
@@ -171,13 +180,16 @@ class Hermite4B200:
         return ek.value + ep.value, ek.value, ep.value
 
     # ---- fused driver / bench entries ----------------------------------------------------------
-    def run(self, atime, t_end, max_steps=0, trace_cap=0, itime0=0.0):
+    def run(self, atime, t_end, max_steps=0, trace_cap=0, itime0=0.0, trace_us=False):
         st = capi.RunStats()
         tn = np.zeros(max(trace_cap, 1), dtype=np.uint32)
         ti = np.zeros(max(trace_cap, 1), dtype=np.float64)
+        tu = np.zeros(max(trace_cap, 1), dtype=np.float32) if trace_us else None
         self._ck(self.lib.gdy_run(self.h, atime, itime0, t_end, max_steps, C.byref(st), _p(tn, _up),
-                                  _p(ti), trace_cap))
+                                  _p(ti), _p(tu, capi._fp), trace_cap))
         k = min(trace_cap, st.iterations)
+        if trace_us:
+            return st, tn[:k], ti[:k], tu[:k]
         return st, tn[:k], ti[:k]
 
     def force_sweep(self, move, want_forces=True):

@@ -61,6 +61,12 @@ int gdy_create(gdy_ctx **out, uint32_t n, double e2, float eta, int device);
  * caller (MPI, torch.distributed, a file, ...).  world == 1 ignores it (may be NULL). */
 int gdy_create_sharded(gdy_ctx **out, uint32_t n, double e2, float eta, int device, int rank,
                        int world, const uint8_t *nccl_uid);
+/* world > 1 with nccl_uid == NULL makes a LOGICAL shard: no communicator, force results are this
+ * shard's partial sums and the caller adds them (single-GPU tests of the sharded path). */
+
+/* Pure host arithmetic (no GPU needed): the particle range [begin, end) whose j-contributions shard
+ * `rank` of `world` computes.  Contiguous, aligned to 64-particle blocks, covering [0, n). */
+int gdy_shard_range(uint32_t n, int rank, int world, uint32_t *begin_out, uint32_t *end_out);
 int gdy_nccl_unique_id(uint8_t *uid_out /* GDY_NCCL_UID_BYTES */);
 int gdy_destroy(gdy_ctx *ctx);
 const char *gdy_last_error(const gdy_ctx *ctx); /* ctx may be NULL: last create() error */
@@ -132,10 +138,11 @@ typedef struct gdy_run_stats
 
 /* Runs the reference loop body (find -> save_old -> predict -> update -> correct -> next time)
  * until ITIME >= t_stop or max_steps block steps (0 = unlimited).  atime = the next block time
- * (from gdy_init_dt or the previous call).  trace_nact/trace_itime (may be NULL) receive the first
- * trace_cap steps. */
+ * (from gdy_init_dt or the previous call).  trace_nact/trace_itime/trace_us (each may be NULL) receive
+ * nact, ITIME and the host wall time in microseconds of the first trace_cap block steps. */
 int gdy_run(gdy_ctx *ctx, double atime, double itime0, double t_stop, uint64_t max_steps,
-            gdy_run_stats *stats, uint32_t *trace_nact, double *trace_itime, uint64_t trace_cap);
+            gdy_run_stats *stats, uint32_t *trace_nact, double *trace_itime, float *trace_us,
+            uint64_t trace_cap);
 
 /* ---- bench / test entry points ---------------------------------------------------------------------- */
 /* Forces of an explicit active list on the current PREDICTED positions (call predicted_pos_vel or

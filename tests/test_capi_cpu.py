@@ -53,7 +53,6 @@ def test_bad_arguments_rejected_before_device_work(lib):
     h = capi._ctx()
     assert lib.gdy_create(C.byref(h), 0, 1e-8, C.c_float(0.01), 0) == capi.GDY_ERR_INVALID
     assert lib.gdy_create_sharded(C.byref(h), 16, 1e-8, C.c_float(0.01), 0, 2, 2, None) == capi.GDY_ERR_INVALID
-    assert lib.gdy_create_sharded(C.byref(h), 16, 1e-8, C.c_float(0.01), 0, 0, 2, None) == capi.GDY_ERR_INVALID
     assert lib.gdy_destroy(None) == 0
     assert lib.gdy_launch_count(None) == 0
     assert lib.gdy_sync(None) == capi.GDY_ERR_INVALID

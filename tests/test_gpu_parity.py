@@ -87,7 +87,7 @@ def test_every_force_variant_matches_oracle(H, O):
     h = H(m, r, v)
     h.init_acc_jrk()
     rng = np.random.default_rng(0)
-    nvariants = 12
+    nvariants = 16
     for variant in range(nvariants):
         for nact in (1, 2, 3, 17, 31, 100, 513, 3001):
             for jsplit in (-1, 1, 5):

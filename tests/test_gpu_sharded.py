@@ -1,0 +1,105 @@
+"""GPU suite: the j-sharded path.
+
+* logical shards on ONE GPU (no communicator): the partial forces of the G shards, added on the host,
+  equal the unsharded result — the same kernels and launch logic the multi-GPU run uses;
+* with >= 2 GPUs: two real shards in one process (two threads), NCCL allreduce inside
+  update_acc_jrk / gdy_run; replicated state must stay BIT-identical on both ranks and follow the
+  single-GPU schedule.
+"""
+import threading
+
+import numpy as np
+import pytest
+
+from gravidy_b200.plummer import plummer
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def H():
+    from gravidy_b200.hermite4 import Hermite4B200
+    return Hermite4B200
+
+
+def rel_err(a, b):
+    da = np.linalg.norm(a[:, :3] - b[:, :3], axis=1) / np.linalg.norm(b[:, :3], axis=1)
+    dj = np.linalg.norm(a[:, 3:] - b[:, 3:], axis=1) / np.linalg.norm(b[:, 3:], axis=1)
+    return max(float(da.max()), float(dj.max()))
+
+
+@pytest.mark.parametrize("world", [2, 3, 8])
+@pytest.mark.parametrize("n", [200, 5000])
+def test_logical_shards_sum_to_unsharded(H, n, world):
+    m, r, v = plummer(n, seed=4, mass_spectrum="salpeter")
+    full = H(m, r, v)
+    full.init_acc_jrk()
+    ref_all = full.download_forces()
+    rng = np.random.default_rng(2)
+    for nact in (1, 7, 100, n):
+        move = np.sort(rng.choice(n, size=nact, replace=False)).astype(np.uint32)
+        ref, _ = full.force_sweep(move)
+        assert rel_err(ref, ref_all[move]) < 1e-12
+        tot = np.zeros((nact, 6))
+        for rank in range(world):
+            h = H(m, r, v, rank=rank, world=world, nccl_uid=None)   # logical shard
+            h.init_acc_jrk()                                        # partial forces of this shard
+            part, _ = h.force_sweep(move)
+            tot += part
+            h.close()
+        assert rel_err(tot, ref) < 1e-12, (n, world, nact)
+
+
+def _two_gpu_available():
+    import torch
+    return torch.cuda.is_available() and torch.cuda.device_count() >= 2
+
+
+@pytest.mark.skipif(not _two_gpu_available(), reason="needs 2 GPUs")
+def test_two_real_shards_nccl(H):
+    n, nsteps = 3000, 60
+    m, r, v = plummer(n, seed=8)
+    single = H(m, r, v)
+    single.init_acc_jrk()
+    at1 = single.init_dt(0.0)
+    st1, tn1, ti1 = single.run(at1, 1e9, max_steps=nsteps, trace_cap=nsteps)
+    s1 = single.get_state()
+
+    uid = H.nccl_unique_id()
+    out, err = [None, None], []
+
+    def work(rank):
+        try:
+            h = H(m, r, v, device=rank, rank=rank, world=2, nccl_uid=uid)
+            h.init_acc_jrk()
+            f0 = h.download_forces()
+            at = h.init_dt(0.0)
+            st, tn, ti = h.run(at, 1e9, max_steps=nsteps, trace_cap=nsteps)
+            out[rank] = (f0, at, st.atime, tn, ti, h.get_state())
+            h.close()
+        except Exception as e:   # noqa: BLE001
+            err.append(e)
+
+    ts = [threading.Thread(target=work, args=(k,)) for k in range(2)]
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join(timeout=300)
+    assert not err, err
+    a, b = out
+    assert np.array_equal(a[0], b[0])                     # allreduce result bit-identical on both ranks
+    assert a[1] == b[1] == at1
+    assert np.array_equal(a[3], b[3]) and np.array_equal(a[4], b[4])
+    for k in a[5]:
+        if k == "p7":
+            continue   # a rank predicts its own j-slice plus the active particles only
+        assert np.array_equal(a[5][k], b[5][k]), k        # replicated state stays bit-identical
+    # ...and the predicted set agrees where both ranks hold a current prediction: each rank's slice
+    # is at the last ITIME on that rank; check the two slices against the single-GPU prediction
+    for rank in range(2):
+        lo, hi = H.shard_range(n, rank, 2)
+        assert np.array_equal(out[rank][5]["p7"][lo:hi, 6], s1["p7"][lo:hi, 6])
+    # and follows the single-GPU run
+    assert np.array_equal(a[3], tn1) and np.array_equal(a[4], ti1) and a[2] == st1.atime
+    np.testing.assert_allclose(a[5]["r4"], s1["r4"], rtol=0, atol=1e-11)
+    assert np.array_equal(a[5]["dt"], s1["dt"])

@@ -14,9 +14,9 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from gravidy_b200.hermite4 import Hermite4B200  # noqa: E402
 from gravidy_b200.plummer import plummer, default_seed  # noqa: E402
 
-NAMES = ["tile_i256", "tile_i128", "tile_i64", "tile_i32", "lane_i16", "lane_i8", "lane_i4", "lane_i2",
-         "lane_i1", "lane_i1x2", "lane_i1x4", "tile_i512"]
-TI = [256, 128, 64, 32, 16, 8, 4, 2, 1, 2, 4, 512]
+NAMES = ["warp_i256", "warp_i128", "warp_i64", "warp_i32", "lane_i16", "lane_i8", "lane_i4", "lane_i2",
+         "lane_i1", "lane_i1x2", "lane_i1x4", "warp_i512", "warp_i128h", "lane_i16x2", "lane_i16x4", "lane_i1x8"]
+TI = [256, 128, 64, 32, 16, 8, 4, 2, 1, 2, 4, 512, 128, 32, 64, 8]
 
 
 def main():
