@@ -29,12 +29,16 @@ class RunStats(C.Structure):
         ("atime", C.c_double),
         ("force_ms", C.c_double),
         ("wall_ms", C.c_double),
+        ("last_nact", C.c_uint32),
+        ("reserved", C.c_uint32),
     ]
 
 
 # every symbol include/gravidy_b200.h declares: name -> (restype, argtypes)
 SIGNATURES = {
     "gdy_abi_version": (C.c_int, []),
+    "gdy_device_count": (C.c_int, []),
+    "gdy_neighbour_distance": (C.c_int, [_ctx, C.c_int, _dp]),
     "gdy_create": (C.c_int, [C.POINTER(_ctx), C.c_uint32, C.c_double, C.c_float, C.c_int]),
     "gdy_create_sharded": (C.c_int, [C.POINTER(_ctx), C.c_uint32, C.c_double, C.c_float, C.c_int,
                                      C.c_int, C.c_int, C.POINTER(C.c_uint8)]),

@@ -146,7 +146,20 @@ int bind_device(gdy_ctx *c) { CU(cudaSetDevice(c->device)); return 0; }
 }  // namespace
 
 // ---- lifetime ------------------------------------------------------------------------------------------
-extern "C" int gdy_abi_version(void) { return 1; }
+extern "C" int gdy_abi_version(void) { return 2; }
+
+extern "C" int gdy_device_count(void)
+{
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess) return 0;
+    int ok = 0;
+    for (int d = 0; d < ndev; ++d)
+    {
+        int major = 0;
+        if (cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, d) == cudaSuccess && major >= 10) ++ok;
+    }
+    return ok;
+}
 
 extern "C" const char *gdy_last_error(const gdy_ctx *c) { return c ? c->err : g_create_err; }
 
@@ -752,6 +765,21 @@ extern "C" int gdy_energy(gdy_ctx *c, double *ekin_out, double *epot_out)
     return GDY_OK;
 }
 
+extern "C" int gdy_neighbour_distance(gdy_ctx *c, int k, double *dist_out)
+{
+    if (!c) return GDY_ERR_INVALID;
+    if (k < 1 || k > KNN_MAX || !dist_out) return fail(c, GDY_ERR_INVALID, "k must be in [1, %d] and dist_out non-NULL", KNN_MAX);
+    BIND(c);
+    int r;
+    if ((r = need_particles(c))) return r;
+    double *d = c->s.part;   // scratch
+    k_knn_distance<<<cdiv(c->n, 128), 128, 0, c->st>>>(c->s, c->n, c->npad, k, d);
+    LAUNCHED(c);
+    CU(cudaMemcpyAsync(dist_out, d, (size_t)c->n * sizeof(double), cudaMemcpyDeviceToHost, c->st));
+    CU(cudaStreamSynchronize(c->st));
+    return GDY_OK;
+}
+
 extern "C" uint64_t gdy_launch_count(const gdy_ctx *c) { return c ? c->launches : 0; }
 
 extern "C" int gdy_sync(gdy_ctx *c)
@@ -776,7 +804,7 @@ extern "C" int gdy_run(gdy_ctx *c, double atime, double itime0, double t_stop, u
     if ((r = need_particles(c))) return r;
     State &s = c->s;
     const auto w0 = std::chrono::steady_clock::now();
-    const bool timed = c->tune_variant == -2 ? false : (stats != nullptr && getenv("GDY_TIME_FORCE") != nullptr);
+    const bool timed = stats != nullptr;   // two event records per block step: force_ms feeds the log's GFLOPS
     uint64_t it = 0, nsteps = 0, inter = 0;
     double force_ms = 0.0;
     double ITIME = itime0, ATIME = atime;
@@ -794,13 +822,17 @@ extern "C" int gdy_run(gdy_ctx *c, double atime, double itime0, double t_stop, u
         const uint32_t nact = c->pin->sched.nact;
         c->last_nact = nact;
         const bool last = !(ITIME < t_stop) || (max_steps && it + 1 >= max_steps);
-        if (nact == 0) return fail(c, GDY_ERR_STATE, "no particle is due at block time %.17g", ITIME);
-
-        if ((r = launch_predict(c, ITIME, nact))) return r;
-        const double *buf; uint32_t ld;
-        if ((r = force_eval(c, nact, s.move, &buf, &ld, timed))) return r;
-        k_correct<<<cdiv(nact, 128), 128, 0, c->st>>>(s, nact, ITIME, (double)c->eta, buf, ld);
-        LAUNCHED(c);
+        // nact == 0 happens in the reference too: on a resumed run init_dt returns the smallest STEP as
+        // the first block time although every particle sits at the snapshot time, so the first pass
+        // through the loop moves nobody and only finds the real next block time.  Same here.
+        const double *buf = nullptr; uint32_t ld = 0;
+        if (nact)
+        {
+            if ((r = launch_predict(c, ITIME, nact))) return r;
+            if ((r = force_eval(c, nact, s.move, &buf, &ld, timed))) return r;
+            k_correct<<<cdiv(nact, 128), 128, 0, c->st>>>(s, nact, ITIME, (double)c->eta, buf, ld);
+            LAUNCHED(c);
+        }
         if ((r = launch_min_time(c))) return r;
         if (last)
         {
@@ -810,7 +842,7 @@ extern "C" int gdy_run(gdy_ctx *c, double atime, double itime0, double t_stop, u
         else if ((r = launch_sched(c, 0.0, true))) return r;
         CU(cudaStreamSynchronize(c->st));
         ATIME = last ? c->pin->atime : c->pin->sched.itime;
-        if (timed)
+        if (timed && nact)
         {
             float ms = 0.f;
             CU(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
@@ -836,6 +868,8 @@ extern "C" int gdy_run(gdy_ctx *c, double atime, double itime0, double t_stop, u
         stats->iterations = it; stats->nsteps = nsteps; stats->interactions = inter;
         stats->itime = ITIME; stats->atime = ATIME; stats->force_ms = force_ms;
         stats->wall_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - w0).count();
+        stats->last_nact = it ? c->last_nact : 0;
+        stats->reserved = 0;
     }
     return GDY_OK;
 }

@@ -410,6 +410,56 @@ k_energy(State s, uint32_t n, uint32_t npad, double *__restrict__ ekin, double *
     }
 }
 
+// ---- k-th nearest neighbour distance ------------------------------------------------------------------
+// The O(N^2) part of the Casertano & Hut density centre (reference: NbodyUtils::get_center_of_density,
+// src/include/utils/NbodyUtils.cpp:163-220, sorts all N distances of every particle on the host).
+// One thread per particle keeps the KNN_MAX smallest squared distances (self excluded) in registers,
+// j through shared-memory tiles.  Padding particles sit 1e10 away and never enter the list.
+constexpr int KNN_MAX = 8;
+__global__ void __launch_bounds__(128)
+k_knn_distance(State s, uint32_t n, uint32_t npad, int k, double *__restrict__ dist)
+{
+    __shared__ double sx[128], sy[128], sz[128];
+    const uint32_t i = blockIdx.x * 128 + threadIdx.x;
+    const uint32_t ic = i < n ? i : n - 1;
+    const double xi = s.x[ic], yi = s.y[ic], zi = s.z[ic];
+    double best[KNN_MAX];
+#pragma unroll
+    for (int q = 0; q < KNN_MAX; ++q) best[q] = 1e300;
+    for (uint32_t t = 0; t < npad; t += 128)
+    {
+        __syncthreads();
+        sx[threadIdx.x] = s.x[t + threadIdx.x];
+        sy[threadIdx.x] = s.y[t + threadIdx.x];
+        sz[threadIdx.x] = s.z[t + threadIdx.x];
+        __syncthreads();
+        for (int j = 0; j < 128; ++j)
+        {
+            const double dx = sx[j] - xi, dy = sy[j] - yi, dz = sz[j] - zi;
+            double r2 = fma(dz, dz, fma(dy, dy, dx * dx));
+            if (t + j == ic) continue;            // self
+            if (r2 < best[KNN_MAX - 1])
+            {
+                // insertion into the sorted list (fully unrolled: stays in registers)
+#pragma unroll
+                for (int q = 0; q < KNN_MAX; ++q)
+                {
+                    const double lo = fmin(best[q], r2);
+                    r2 = fmax(best[q], r2);
+                    best[q] = lo;
+                }
+            }
+        }
+    }
+    if (i < n)
+    {
+        double r2 = best[0];
+#pragma unroll
+        for (int q = 1; q < KNN_MAX; ++q) if (q == k - 1) r2 = best[q];
+        dist[i] = __dsqrt_rn(r2);
+    }
+}
+
 // Deterministic sum of two arrays (fixed tree): out[0] = sum a, out[1] = sum b.  One block.
 __global__ void __launch_bounds__(1024) k_sum2(const double *a, const double *b, uint32_t n, double *out)
 {

@@ -179,6 +179,11 @@ class Hermite4B200:
         self._ck(self.lib.gdy_energy(self.h, C.byref(ek), C.byref(ep)))
         return ek.value + ep.value, ek.value, ep.value
 
+    def neighbour_distance(self, k):
+        out = np.empty(self.n)
+        self._ck(self.lib.gdy_neighbour_distance(self.h, k, _p(out)))
+        return out
+
     # ---- fused driver / bench entries ----------------------------------------------------------
     def run(self, atime, t_end, max_steps=0, trace_cap=0, itime0=0.0, trace_us=False):
         st = capi.RunStats()

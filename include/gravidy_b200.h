@@ -43,6 +43,10 @@ typedef enum gdy_status
 /* Version of this ABI (bumped on any signature change). */
 int gdy_abi_version(void);
 
+/* Number of usable sm_100 devices (0 if none or no driver): replaces cudaGetDeviceCount in
+ * Hermite4GPU::Hermite4GPU (reference: src/include/gpu/Hermite4GPU.cu:50-60). */
+int gdy_device_count(void);
+
 /* ---- lifetime ------------------------------------------------------------------------------
  * Replaces Hermite4GPU::Hermite4GPU / alloc_arrays_device / ~Hermite4GPU
  * (reference: src/include/gpu/Hermite4GPU.cu:43-194).
@@ -124,6 +128,11 @@ int gdy_next_integration_time(gdy_ctx *ctx, double *atime_out);
  * CPU: src/include/utils/NbodyUtils.cpp:427-529).  Unsoftened potential. */
 int gdy_energy(gdy_ctx *ctx, double *ekin_out, double *epot_out);
 
+/* Distance of every particle to its k-th nearest neighbour (1 <= k <= 8) at the current positions:
+ * the O(N^2) part of NbodyUtils::get_center_of_density (reference: src/include/utils/NbodyUtils.cpp:
+ * 163-220, which sorts all N distances per particle on the host).  dist_out = n doubles. */
+int gdy_neighbour_distance(gdy_ctx *ctx, int k, double *dist_out);
+
 /* ---- fused drivers (same arithmetic as the hooks, fewer launches / host round trips) -------------- */
 typedef struct gdy_run_stats
 {
@@ -134,6 +143,8 @@ typedef struct gdy_run_stats
     double atime;          /* next block time                        */
     double force_ms;       /* device time in the force kernels       */
     double wall_ms;        /* host wall time of the call             */
+    uint32_t last_nact;    /* nact of the last completed block step  */
+    uint32_t reserved;
 } gdy_run_stats;
 
 /* Runs the reference loop body (find -> save_old -> predict -> update -> correct -> next time)

@@ -257,6 +257,10 @@ class RefOracle(_Base):
     def normalize_dt(self, new_dt, old_dt, t):
         return self.lib.gref_normalize_dt(self.h, new_dt, old_dt, t)
 
+    def set_print_options(self, print_all=False, print_lagrange=False):
+        self.lib.gref_set_print_options.argtypes = [C.c_void_p, C.c_int, C.c_int]
+        self.lib.gref_set_print_options(self.h, int(print_all), int(print_lagrange))
+
     def integration(self):
         """The reference's own driver: writes <workdir>/run.out.{info,log,snapshot_*}."""
         self.lib.gref_integration(self.h)

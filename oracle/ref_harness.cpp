@@ -132,6 +132,14 @@ double gref_normalize_dt(gref *g, double new_dt, double old_dt, double t)
 // The reference's own driver, unmodified: writes <prefix>.out.{info,log,snapshot_*}.
 void gref_integration(gref *g) { g->h4->integration(); }
 
+// -a / -l of the command line (OptionsParser.cpp:372-376): all-particle dumps and Lagrange radii at
+// every output point.
+void gref_set_print_options(gref *g, int print_all, int print_lagrange)
+{
+    g->ns->ops.print_all = print_all;
+    g->ns->ops.print_lagrange = print_lagrange;
+}
+
 // ---- state copy-out / copy-in (plain doubles; NULL pointers are skipped) -------------------
 // r4: n x {x,y,z,m}   v4: n x {x,y,z,0}   f6/old6: n x {a[3],a1[3]}   a2/a3: n x 3
 // p7: n x {r[3],v[3],m} with m widened from float       move: n x uint32

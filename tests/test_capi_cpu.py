@@ -35,7 +35,7 @@ def test_header_symbols_all_exported(lib):
 
 
 def test_abi_version(lib):
-    assert lib.gdy_abi_version() == 1
+    assert lib.gdy_abi_version() == 2
 
 
 def test_no_cpu_fallback(lib):
