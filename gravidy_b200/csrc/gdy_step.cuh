@@ -26,24 +26,28 @@ __device__ __forceinline__ double dvd(double a, double b) { return __ddiv_rn(a, 
 // (reference: src/include/cpu/Hermite4CPU.cpp:346-359): dt2 = dt*dt, dt3 = dt2*dt, dt2/2.0, dt3/6.0,
 // ((dt3c*j + dt2c*a) + dt*v) + r and (dt2c*j + dt*a) + v.
 struct Pred6 { double x, y, z, vx, vy, vz; };
-__device__ __forceinline__ Pred6 predict_one(const State &s, uint32_t i, double itime)
+__device__ __forceinline__ Pred6 predict_vals(double itime, double t, double x, double y, double z, double vx,
+                                              double vy, double vz, double ax, double ay, double az,
+                                              double jx, double jy, double jz)
 {
-    const double dt = sub(itime, s.t[i]);
+    const double dt = sub(itime, t);
     const double dt2 = mul(dt, dt);
     const double dt3 = mul(dt2, dt);
     const double dt2c = dvd(dt2, 2.0);
     const double dt3c = dvd(dt3, 6.0);
-    const double ax = s.f[0][i], ay = s.f[1][i], az = s.f[2][i];
-    const double jx = s.f[3][i], jy = s.f[4][i], jz = s.f[5][i];
-    const double vx = s.vx[i], vy = s.vy[i], vz = s.vz[i];
     Pred6 p;
-    p.x = add(add(add(mul(dt3c, jx), mul(dt2c, ax)), mul(dt, vx)), s.x[i]);
-    p.y = add(add(add(mul(dt3c, jy), mul(dt2c, ay)), mul(dt, vy)), s.y[i]);
-    p.z = add(add(add(mul(dt3c, jz), mul(dt2c, az)), mul(dt, vz)), s.z[i]);
+    p.x = add(add(add(mul(dt3c, jx), mul(dt2c, ax)), mul(dt, vx)), x);
+    p.y = add(add(add(mul(dt3c, jy), mul(dt2c, ay)), mul(dt, vy)), y);
+    p.z = add(add(add(mul(dt3c, jz), mul(dt2c, az)), mul(dt, vz)), z);
     p.vx = add(add(mul(dt2c, jx), mul(dt, ax)), vx);
     p.vy = add(add(mul(dt2c, jy), mul(dt, ay)), vy);
     p.vz = add(add(mul(dt2c, jz), mul(dt, az)), vz);
     return p;
+}
+__device__ __forceinline__ Pred6 predict_one(const State &s, uint32_t i, double itime)
+{
+    return predict_vals(itime, s.t[i], s.x[i], s.y[i], s.z[i], s.vx[i], s.vy[i], s.vz[i], s.f[0][i], s.f[1][i],
+                        s.f[2][i], s.f[3][i], s.f[4][i], s.f[5][i]);
 }
 
 __device__ __forceinline__ void store_pred(const State &s, uint32_t i, const Pred6 &p)
@@ -148,71 +152,105 @@ __device__ __forceinline__ double normalize_dt(double new_dt, double old_dt, dou
 // produced and stored to h_f here, and the forces they replace are saved to h_old on the way — the
 // scatter at the end of update_acc_jrk and save_old_acc_jrk (reference: src/include/Hermite4.cpp:145-153)
 // fused into the corrector; same values, two launches fewer.
-__global__ void k_correct(State s, uint32_t nact, double itime, double eta,
-                          const double *__restrict__ fbuf, uint32_t ld)
+// The arithmetic of one particle: old forces (oa, oj), new forces (fa, fj), old step dt1, predicted p.
+// Writes a2, a3, r, v, t, dt of particle i and returns the new step.
+struct CorrIn { double dt1; double oa[3], oj[3], fa[3], fj[3]; Pred6 p; };
+__device__ __forceinline__ double correct_core(const State &s, uint32_t i, double itime, double eta, const CorrIn &q)
 {
-    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
-    if (k >= nact) return;
-    const uint32_t i = s.move[k];
-
-    const double dt1 = s.dt[i];
+    const double dt1 = q.dt1;
     const double dt2 = mul(dt1, dt1);
     const double dt3 = mul(dt2, dt1);
     const double dt4 = mul(dt2, dt2);
     const double dt5 = mul(dt4, dt1);
     const double c4_24 = dvd(dt4, 24.0), c5_120 = dvd(dt5, 120.0), c3_6 = dvd(dt3, 6.0);
 
-    double a2[3], a3[3], fa[3], fj[3];
+    double a2[3], a3[3];
 #pragma unroll
     for (int c = 0; c < 3; ++c)
     {
-        double oa, oj;
-        if (fbuf)
-        {
-            oa = s.f[c][i]; oj = s.f[3 + c][i];
-            s.old[c][i] = oa; s.old[3 + c][i] = oj;
-            fa[c] = fbuf[(size_t)c * ld + k];
-            fj[c] = fbuf[(size_t)(3 + c) * ld + k];
-            s.f[c][i] = fa[c];
-            s.f[3 + c][i] = fj[c];
-        }
-        else
-        {
-            oa = s.old[c][i]; oj = s.old[3 + c][i];
-            fa[c] = s.f[c][i];
-            fj[c] = s.f[3 + c][i];
-        }
-        const double d = sub(oa, fa[c]);
+        const double d = sub(q.oa[c], q.fa[c]);
         // (-6*(old.a - f.a) - dt1*(4*old.a1 + 2*f.a1)) / dt2
-        a2[c] = dvd(sub(mul(-6.0, d), mul(dt1, add(mul(4.0, oj), mul(2.0, fj[c])))), dt2);
+        a2[c] = dvd(sub(mul(-6.0, d), mul(dt1, add(mul(4.0, q.oj[c]), mul(2.0, q.fj[c])))), dt2);
         // (12*(old.a - f.a) + 6*dt1*(old.a1 + f.a1)) / dt3
-        a3[c] = dvd(add(mul(12.0, d), mul(mul(6.0, dt1), add(oj, fj[c]))), dt3);
+        a3[c] = dvd(add(mul(12.0, d), mul(mul(6.0, dt1), add(q.oj[c], q.fj[c]))), dt3);
         s.a2[c][i] = a2[c];
         s.a3[c][i] = a3[c];
     }
     // r = p.r + (dt4/24)*a2 + (dt5/120)*a3 ;  v = p.v + (dt3/6)*a2 + (dt4/24)*a3
-    const double *pp = s.pb + pbidx(i, 0);
-    s.x[i] = add(add(pp[0], mul(c4_24, a2[0])), mul(c5_120, a3[0]));
-    s.y[i] = add(add(pp[JB], mul(c4_24, a2[1])), mul(c5_120, a3[1]));
-    s.z[i] = add(add(pp[2 * JB], mul(c4_24, a2[2])), mul(c5_120, a3[2]));
-    s.vx[i] = add(add(pp[3 * JB], mul(c3_6, a2[0])), mul(c4_24, a3[0]));
-    s.vy[i] = add(add(pp[4 * JB], mul(c3_6, a2[1])), mul(c4_24, a3[1]));
-    s.vz[i] = add(add(pp[5 * JB], mul(c3_6, a2[2])), mul(c4_24, a3[2]));
+    s.x[i] = add(add(q.p.x, mul(c4_24, a2[0])), mul(c5_120, a3[0]));
+    s.y[i] = add(add(q.p.y, mul(c4_24, a2[1])), mul(c5_120, a3[1]));
+    s.z[i] = add(add(q.p.z, mul(c4_24, a2[2])), mul(c5_120, a3[2]));
+    s.vx[i] = add(add(q.p.vx, mul(c3_6, a2[0])), mul(c4_24, a3[0]));
+    s.vy[i] = add(add(q.p.vy, mul(c3_6, a2[1])), mul(c4_24, a3[1]));
+    s.vz[i] = add(add(q.p.vz, mul(c3_6, a2[2])), mul(c4_24, a3[2]));
     s.t[i] = itime;
 
     // get_timestep_normal(i, eta): h_dt[i] is still the old step here
     const double ax1_2 = add(a2[0], mul(dt1, a3[0]));
     const double ay1_2 = add(a2[1], mul(dt1, a3[1]));
     const double az1_2 = add(a2[2], mul(dt1, a3[2]));
-    const double abs_a1 = magnitude(fa[0], fa[1], fa[2]);
-    const double abs_j1 = magnitude(fj[0], fj[1], fj[2]);
+    const double abs_a1 = magnitude(q.fa[0], q.fa[1], q.fa[2]);
+    const double abs_j1 = magnitude(q.fj[0], q.fj[1], q.fj[2]);
     const double abs_j12 = mul(abs_j1, abs_j1);
     const double abs_a1_3 = magnitude(a3[0], a3[1], a3[2]);
     const double abs_a1_2 = magnitude(ax1_2, ay1_2, az1_2);
     const double abs_a1_22 = mul(abs_a1_2, abs_a1_2);
     const double normal_dt = __dsqrt_rn(
         mul(eta, dvd(add(mul(abs_a1, abs_a1_2), abs_j12), add(mul(abs_j1, abs_a1_3), abs_a1_22))));
-    s.dt[i] = normalize_dt(normal_dt, dt1, itime);
+    const double ndt = normalize_dt(normal_dt, dt1, itime);
+    s.dt[i] = ndt;
+    return ndt;
+}
+
+__global__ void k_correct(State s, uint32_t nact, double itime, double eta,
+                          const double *__restrict__ fbuf, uint32_t ld)
+{
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= nact) return;
+    const uint32_t i = s.move[k];
+    CorrIn q;
+    q.dt1 = s.dt[i];
+#pragma unroll
+    for (int c = 0; c < 3; ++c)
+    {
+        if (fbuf)
+        {
+            q.oa[c] = s.f[c][i]; q.oj[c] = s.f[3 + c][i];
+            s.old[c][i] = q.oa[c]; s.old[3 + c][i] = q.oj[c];
+            q.fa[c] = fbuf[(size_t)c * ld + k];
+            q.fj[c] = fbuf[(size_t)(3 + c) * ld + k];
+            s.f[c][i] = q.fa[c];
+            s.f[3 + c][i] = q.fj[c];
+        }
+        else
+        {
+            q.oa[c] = s.old[c][i]; q.oj[c] = s.old[3 + c][i];
+            q.fa[c] = s.f[c][i];
+            q.fj[c] = s.f[3 + c][i];
+        }
+    }
+    const double *pp = s.pb + pbidx(i, 0);
+    q.p = Pred6{pp[0], pp[JB], pp[2 * JB], pp[3 * JB], pp[4 * JB], pp[5 * JB]};
+    correct_core(s, i, itime, eta, q);
+}
+
+// Persistent-kernel flavour: the forces being replaced are read past L1 (another SM may have written
+// them a few steps ago), the new ones come in registers; save-old and the force store are fused in.
+__device__ __forceinline__ double correct_one(const State &s, uint32_t i, double itime, double eta,
+                                              const Pred6 &p, const double *f /* [6] */)
+{
+    CorrIn q;
+    q.dt1 = __ldcg(s.dt + i);
+#pragma unroll
+    for (int c = 0; c < 3; ++c)
+    {
+        q.oa[c] = __ldcg(s.f[c] + i); q.oj[c] = __ldcg(s.f[3 + c] + i);
+        s.old[c][i] = q.oa[c]; s.old[3 + c][i] = q.oj[c];
+        q.fa[c] = f[c]; q.fj[c] = f[3 + c];
+        s.f[c][i] = f[c]; s.f[3 + c][i] = f[3 + c];
+    }
+    q.p = p;
+    return correct_core(s, i, itime, eta, q);
 }
 
 // ---- scheduler -----------------------------------------------------------------------------------

@@ -1,0 +1,106 @@
+#!/usr/bin/env python
+"""Block-timestep integration of a seeded Plummer model through the fused driver (gdy_run): the
+BASELINE.json configs 2-4 (N=16k equal mass, N=64k Salpeter, N=256k j-sharded over 1/2/4/8 GPUs).
+
+Prints ONE JSON line: block steps, sum of nact, pairs, wall seconds of the `while` loop (SURVEY.md 8d:
+init_acc_jrk, the energy diagnostic and nbody_attributes are outside the window on both sides),
+GFLOP/s at 60 flop/pair, the energy error at the end, and the per-nact-bin step times.
+
+    python tools/integrate.py --n 16384 --t 1
+    python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 tools/integrate.py --n 262144 --t 1
+"""
+import argparse
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from gravidy_b200.hermite4 import Hermite4B200  # noqa: E402
+from gravidy_b200.plummer import plummer, default_seed  # noqa: E402
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--n", type=int, default=16384)
+    ap.add_argument("--t", type=float, default=1.0)
+    ap.add_argument("--spectrum", default="equal")
+    ap.add_argument("--softening", type=float, default=1e-4)
+    ap.add_argument("--eta", type=float, default=0.01)
+    ap.add_argument("--max-steps", type=int, default=0)
+    ap.add_argument("--trace", type=int, default=400000)
+    ap.add_argument("--out", default="")
+    a = ap.parse_args()
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    uid = None
+    dist = None
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local)
+        dev = torch.device("cuda", local)
+        dist.init_process_group("nccl", device_id=dev)
+        t = torch.zeros(128, dtype=torch.uint8, device=dev)
+        if rank == 0:
+            t.copy_(torch.frombuffer(bytearray(Hermite4B200.nccl_unique_id()), dtype=torch.uint8))
+        dist.broadcast(t, 0)
+        uid = bytes(t.cpu().numpy().tobytes())
+
+    m, r, v = plummer(a.n, seed=default_seed(a.n), mass_spectrum=a.spectrum)
+    h = Hermite4B200(m, r, v, softening=a.softening, eta=a.eta, device=local, rank=rank, world=world,
+                     nccl_uid=uid)
+    t0 = time.perf_counter()
+    h.init_acc_jrk()
+    h.sync()
+    t_init = time.perf_counter() - t0
+    at = h.init_dt(0.0)
+    t0 = time.perf_counter()
+    e0 = h.get_energy()
+    t_energy = time.perf_counter() - t0
+    if dist is not None:
+        dist.barrier()
+    st, tn, ti, tu = h.run(at, a.t, max_steps=a.max_steps, trace_cap=a.trace, trace_us=True)
+    h.sync()
+    wall = st.wall_ms * 1e-3
+    if dist is not None:
+        import torch
+        tt = torch.tensor([wall], dtype=torch.float64, device=torch.device("cuda", local))
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        wall = float(tt.item())
+    e1 = h.get_energy()
+    bins = []
+    edges = [0, 1, 2, 4, 8, 16, 32, 64, 128, 256, 512, 1024, 4096, 16384, 65536, 1 << 30]
+    for lo, hi in zip(edges[:-1], edges[1:]):
+        sel = (tn > lo) & (tn <= hi)
+        if sel.any():
+            bins.append({"nact": [lo, hi], "steps": int(sel.sum()), "median_us": float(np.median(tu[sel])),
+                         "share_of_wall": float(tu[sel].sum() / tu.sum())})
+    line = {
+        "tool": "integrate", "n": a.n, "n_gpus": world, "spectrum": a.spectrum, "softening": a.softening,
+        "eta": a.eta, "t_end": a.t, "t_reached": st.itime, "block_steps": int(st.iterations),
+        "sum_nact": int(st.nsteps), "pairs": int(st.interactions), "wall_s": wall,
+        "wall_s_per_nbu": wall / st.itime if st.itime > 0 else None,
+        "us_per_block_step": wall / max(int(st.iterations), 1) * 1e6,
+        "pairs_per_s": st.interactions / wall, "gflops_60": st.interactions / wall * 60 / 1e9,
+        "force_kernel_s": st.force_ms * 1e-3,
+        "e0": e0[0], "e1": e1[0], "cum_rel_energy_error": abs((e1[0] - e0[0]) / e0[0]),
+        "init_acc_jrk_s": t_init, "energy_s": t_energy, "launches": h.launch_count(), "bins": bins,
+    }
+    if rank == 0:
+        s = json.dumps(line)
+        print(s, flush=True)
+        if a.out:
+            with open(a.out, "w") as f:
+                f.write(s + "\n")
+    h.close()
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
