@@ -9,6 +9,7 @@
 #include "../../include/gravidy_b200.h"
 #include "gdy_force.cuh"
 #include "gdy_step.cuh"
+#include "gdy_persist.cuh"
 
 #include <chrono>
 #include <cmath>
@@ -102,6 +103,23 @@ struct gdy_ctx
     bool have_particles = false, have_pred = false;
     uint64_t launches = 0;
     double force_ms_acc = 0.0;
+
+    // persistent small-step kernel (gdy_persist.cuh)
+    uint32_t ps_nact_max = 0;        // 0 = off
+    uint32_t ps_grid = 0, ps_slice = 0, ps_gpad = 0;
+    double *ps_part = nullptr, *ps_cta_min = nullptr, *ps_act_next = nullptr;
+    uint32_t *ps_cta_cnt = nullptr, *ps_cta_list = nullptr, *ps_bar = nullptr;
+    PersistCtl *ps_ctl = nullptr, *ps_ctl_host = nullptr;
+    TraceRec *ps_trace = nullptr, *ps_trace_host = nullptr;
+    uint32_t ps_seq = 0, ps_xseq = 0;
+    bool ps_last = false;            // the last block step was done by the persistent kernel
+    // peer-memory exchange of the persistent path (world > 1)
+    bool peers_ok = false;
+    double *xbuf = nullptr;          // my exchange buffer: slots then flags
+    double *xslot[PS_MAX_WORLD] = {};
+    uint32_t *xflag[PS_MAX_WORLD] = {};
+    void *xopened[PS_MAX_WORLD] = {};
+    uint64_t ps_steps_total = 0, ps_launches = 0;
     char err[512] = "";
 };
 
@@ -178,6 +196,8 @@ extern "C" int gdy_nccl_unique_id(uint8_t *uid_out)
 namespace {
 
 constexpr size_t PART_MIN_DOUBLES = (size_t)8 << 20;   // 64 MiB of j-split partials at least
+constexpr uint32_t PS_STEPS_MAX = 4096;                // block steps per persistent launch
+constexpr uint32_t PS_DEFAULT_NACT = 64;               // active sets up to this size go to the persistent kernel
 
 int alloc_all(gdy_ctx *c)
 {
@@ -235,6 +255,35 @@ int alloc_all(gdy_ctx *c)
     k_init_pb<<<cdiv(c->npad, 256), 256, 0, c->st>>>(s, c->n, c->npad);
     LAUNCHED(c);
     CU(force_variants_prepare());
+    // persistent small-step kernel: one CTA per SM, co-resident (cooperative launch)
+    {
+        int coop = 0, per_sm = 0;
+        CU(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, c->device));
+        CU(cudaFuncSetAttribute((const void *)k_persist_steps<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PersistSmem)));
+        CU(cudaFuncSetAttribute((const void *)k_persist_steps<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PersistSmem)));
+        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, (const void *)k_persist_steps<false>, PS_T, sizeof(PersistSmem)));
+        c->ps_grid = (uint32_t)c->num_sms;
+        if (c->ps_grid > (uint32_t)PS_GMAX) c->ps_grid = PS_GMAX;
+        c->ps_slice = cdiv(c->n, c->ps_grid);
+        c->ps_gpad = round_up(c->ps_grid, 32);
+        CU(cudaMalloc(&c->ps_part, (size_t)PS_NACT_CAP * 6 * c->ps_gpad * sizeof(double)));
+        CU(cudaMalloc(&c->ps_cta_min, c->ps_grid * sizeof(double)));
+        CU(cudaMalloc(&c->ps_act_next, PS_NACT_CAP * sizeof(double)));
+        CU(cudaMalloc(&c->ps_cta_cnt, c->ps_grid * sizeof(uint32_t)));
+        CU(cudaMalloc(&c->ps_cta_list, (size_t)c->ps_grid * c->ps_slice * sizeof(uint32_t)));
+        CU(cudaMalloc(&c->ps_bar, 128));
+        CU(cudaMalloc(&c->ps_ctl, sizeof(PersistCtl)));
+        CU(cudaMalloc(&c->ps_trace, PS_STEPS_MAX * sizeof(TraceRec)));
+        CU(cudaHostAlloc(&c->ps_ctl_host, sizeof(PersistCtl), cudaHostAllocDefault));
+        CU(cudaHostAlloc(&c->ps_trace_host, PS_STEPS_MAX * sizeof(TraceRec), cudaHostAllocDefault));
+        memset(c->ps_ctl_host, 0, sizeof(PersistCtl));
+        uint32_t def = PS_DEFAULT_NACT;
+        if (const char *e = getenv("GDY_PERSIST_NACT")) def = (uint32_t)atoi(e);
+        if (def > (uint32_t)PS_NACT_CAP) def = PS_NACT_CAP;
+        if (!coop || per_sm < 1) def = 0;
+        // sharded contexts join the persistent path once their peers are attached (gdy_peer_attach)
+        c->ps_nact_max = c->world == 1 ? def : 0;
+    }
     for (int v = 0; v < FV_COUNT; ++v)
         CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&c->occ[v], (const void *)g_variants[v].fn[0],
                                                          g_variants[v].threads, g_variants[v].smem));
@@ -328,6 +377,10 @@ extern "C" int gdy_destroy(gdy_ctx *c)
     cudaFree(c->pool); cudaFree(c->d_move); cudaFree(c->d_ilist); cudaFree(c->d_block_cnt);
     cudaFree(c->d_block_min); cudaFree(c->d_sched); cudaFree(c->d_atime); cudaFree(c->d_energy);
     cudaFree(c->d_stage); cudaFree(c->d_counter);
+    cudaFree(c->ps_part); cudaFree(c->ps_cta_min); cudaFree(c->ps_act_next); cudaFree(c->ps_cta_cnt);
+    cudaFree(c->ps_cta_list); cudaFree(c->ps_bar); cudaFree(c->ps_ctl); cudaFree(c->ps_trace);
+    if (c->ps_ctl_host) cudaFreeHost(c->ps_ctl_host);
+    if (c->ps_trace_host) cudaFreeHost(c->ps_trace_host);
     if (c->pin) cudaFreeHost(c->pin);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
@@ -790,6 +843,69 @@ extern "C" int gdy_sync(gdy_ctx *c)
     return GDY_OK;
 }
 
+// ---- persistent small-step launches ------------------------------------------------------------------------
+namespace {
+
+// Runs block steps inside ONE cooperative launch while the active set stays <= ps_nact_max (see
+// gdy_persist.cuh).  Entry: ATIME = `itime` with its active list in State.move[0..nact).  Returns with
+// the pinned PersistCtl filled in; State.move then holds the list of the first step NOT done.
+int run_persist(gdy_ctx *c, double itime, uint32_t nact, double t_stop, uint32_t budget, bool timed, float *ms_out)
+{
+    PersistArgs a{};
+    a.s = c->s; a.n = c->n;
+    a.jb = c->blk_begin * JB;
+    a.je = c->blk_end * JB < c->n ? c->blk_end * JB : c->n;
+    if (a.je < a.jb) a.je = a.jb;
+    a.e2 = c->e2; a.eta = (double)c->eta; a.t_stop = t_stop;
+    a.entry_itime = itime; a.entry_nact = nact;
+    a.max_steps = budget < PS_STEPS_MAX ? budget : PS_STEPS_MAX;
+    a.nact_max = c->ps_nact_max;
+    a.slice = c->ps_slice; a.seq = ++c->ps_seq;
+    a.part = c->ps_part; a.gpad = c->ps_gpad; a.cta_min = c->ps_cta_min; a.cta_cnt = c->ps_cta_cnt;
+    a.cta_list = c->ps_cta_list; a.act_next = c->ps_act_next; a.bar = c->ps_bar;
+    a.ctl_dev = c->ps_ctl; a.ctl_host = c->ps_ctl_host; a.trace = c->ps_trace;
+    a.rank = c->rank; a.world = c->peers_ok ? c->world : 1;
+    a.xseq0 = c->ps_xseq;
+    for (int r = 0; r < PS_MAX_WORLD; ++r) { a.xslot[r] = c->xslot[r]; a.xflag[r] = c->xflag[r]; }
+    CU(cudaMemsetAsync(c->ps_bar, 0, sizeof(uint32_t), c->st));
+    if (timed) CU(cudaEventRecord(c->ev0, c->st));
+    void *args[] = {&a};
+    const void *fn = c->mask_self ? (const void *)k_persist_steps<true> : (const void *)k_persist_steps<false>;
+    CU(cudaLaunchCooperativeKernel(fn, dim3(c->ps_grid), dim3(PS_T), args, sizeof(PersistSmem), c->st));
+    ++c->launches; ++c->ps_launches;
+    if (timed) CU(cudaEventRecord(c->ev1, c->st));
+    CU(cudaStreamSynchronize(c->st));
+    if (c->ps_ctl_host->seq != a.seq) return fail(c, GDY_ERR_STATE, "persistent kernel left no result (seq %u != %u)", c->ps_ctl_host->seq, a.seq);
+    c->ps_xseq += c->ps_ctl_host->steps;
+    c->ps_steps_total += c->ps_ctl_host->steps;
+    if (ms_out)
+    {
+        *ms_out = 0.f;
+        if (timed) CU(cudaEventElapsedTime(ms_out, c->ev0, c->ev1));
+    }
+    return 0;
+}
+
+}  // namespace
+
+extern "C" int gdy_set_persist(gdy_ctx *c, int nact_max)
+{
+    if (!c) return GDY_ERR_INVALID;
+    if (nact_max > PS_NACT_CAP) return fail(c, GDY_ERR_INVALID, "nact_max %d > %d", nact_max, (int)PS_NACT_CAP);
+    if (c->world > 1 && !c->peers_ok && nact_max != 0)
+        return fail(c, GDY_ERR_STATE, "a sharded context needs gdy_peer_attach before the persistent path");
+    c->ps_nact_max = nact_max < 0 ? PS_DEFAULT_NACT : (uint32_t)nact_max;
+    return GDY_OK;
+}
+
+extern "C" int gdy_persist_stats(const gdy_ctx *c, uint64_t *launches_out, uint64_t *steps_out)
+{
+    if (!c) return GDY_ERR_INVALID;
+    if (launches_out) *launches_out = c->ps_launches;
+    if (steps_out) *steps_out = c->ps_steps_total;
+    return GDY_OK;
+}
+
 // ---- fused driver ----------------------------------------------------------------------------------------
 // The reference loop body (src/include/cpu/Hermite4CPU_integration.cpp:81-124) with everything on the
 // device and ONE host readback per block step ({next block time, next nact}, 16 bytes of pinned
@@ -818,8 +934,49 @@ extern "C" int gdy_run(gdy_ctx *c, double atime, double itime0, double t_stop, u
     while (ITIME < t_stop)
     {
         if (max_steps && it >= max_steps) break;
-        ITIME = ATIME;
         const uint32_t nact = c->pin->sched.nact;
+        if (c->ps_nact_max && nact && nact <= c->ps_nact_max)
+        {
+            // small active set: stay on the device until a big block (or t_stop / the step budget) comes up
+            const uint64_t left = max_steps ? max_steps - it : PS_STEPS_MAX;
+            const uint32_t budget = (uint32_t)(left < PS_STEPS_MAX ? left : PS_STEPS_MAX);
+            float ms = 0.f;
+            if ((r = run_persist(c, ATIME, nact, t_stop, budget, timed, &ms))) return r;
+            const PersistCtl pc = *c->ps_ctl_host;
+            if (pc.steps == 0) return fail(c, GDY_ERR_STATE, "persistent kernel made no progress");
+            force_ms += ms;
+            if (it < trace_cap && (trace_nact || trace_itime || trace_us))
+            {
+                const uint64_t k = pc.steps < trace_cap - it ? pc.steps : trace_cap - it;
+                CU(cudaMemcpyAsync(c->ps_trace_host, c->ps_trace, k * sizeof(TraceRec), cudaMemcpyDeviceToHost, c->st));
+                CU(cudaStreamSynchronize(c->st));
+                const auto now = std::chrono::steady_clock::now();
+                const float us = std::chrono::duration<float, std::micro>(now - tick).count() / (float)pc.steps;
+                tick = now;
+                for (uint64_t q = 0; q < k; ++q)
+                {
+                    if (trace_nact) trace_nact[it + q] = c->ps_trace_host[q].nact;
+                    if (trace_itime) trace_itime[it + q] = c->ps_trace_host[q].itime;
+                    if (trace_us) trace_us[it + q] = us;
+                }
+            }
+            else tick = std::chrono::steady_clock::now();
+            it += pc.steps; nsteps += pc.sum_nact; inter += pc.sum_nact * (uint64_t)c->n;
+            ITIME = pc.last_itime; ATIME = pc.atime;
+            c->last_nact = pc.last_nact;
+            c->pin->sched.nact = pc.nact_next;
+            c->pin->sched.itime = pc.atime;
+            c->ps_last = true;
+            if (pc.steps >= budget && ITIME < t_stop && !(max_steps && it >= max_steps))
+            {
+                // stopped on the per-launch step cap: State.move still holds the last completed step's list
+                if ((r = launch_sched(c, ATIME, false))) return r;
+                CU(cudaStreamSynchronize(c->st));
+            }
+            continue;
+        }
+        c->ps_last = false;
+        ITIME = ATIME;
         c->last_nact = nact;
         const bool last = !(ITIME < t_stop) || (max_steps && it + 1 >= max_steps);
         // nact == 0 happens in the reference too: on a resumed run init_dt returns the smallest STEP as
@@ -862,6 +1019,15 @@ extern "C" int gdy_run(gdy_ctx *c, double atime, double itime0, double t_stop, u
         inter += (uint64_t)nact * (uint64_t)c->n;
         nsteps += nact;
         ++it;
+    }
+    if (c->ps_last)
+    {
+        // h_p as the reference leaves it: the persistent kernel predicts on the fly and stores only the
+        // active particles' predictions; the others are recomputed here (same arithmetic, same bits)
+        k_predict_rest<<<cdiv(c->n, 256), 256, 0, c->st>>>(s, c->n, ITIME);
+        LAUNCHED(c);
+        c->have_pred = true;
+        c->ps_last = false;
     }
     if (stats)
     {

@@ -246,7 +246,12 @@ k_persist_steps(const PersistArgs a)
             if (tid == 0) sm.total = tot;
             __syncthreads();
             nact = sm.total;
-            // my own segment of h_move (always current, so the host loop can take over at any step)
+            // my own segment of h_move, so that the host loop can take over at any step — unless this launch
+            // ends on its step budget or t_stop: then h_move keeps the list of the last COMPLETED step, as the
+            // reference leaves it (src/include/Hermite4.cpp:63-84), and the host re-runs the scheduler if it
+            // goes on
+            const bool stop_end = steps >= a.max_steps || !(last_itime < a.t_stop);
+            if (!stop_end)
             {
                 const uint32_t mycnt = (cta + 1 < G ? sm.cnt[cta + 1] : nact) - sm.cnt[cta];
                 const uint32_t off = sm.cnt[cta];
@@ -324,7 +329,6 @@ k_persist_steps(const PersistArgs a)
             __syncthreads();
             // outputs o = (q, c, il): fold the warps in fixed order -> part[k][c][cta]
             const int ILW = IL < 32 ? IL : 32;
-            const int nwarp_rows = IL < 32 ? PS_W : PS_W;   // every warp holds j-lanes of every il
             for (int o = tid; o < 2 * 6 * ILW; o += PS_T)
             {
                 const int il = o % ILW, c = (o / ILW) % 6, q = o / (6 * ILW);
@@ -332,7 +336,7 @@ k_persist_steps(const PersistArgs a)
                 if (kloc < nk)
                 {
                     double sum = 0.0;
-                    for (int ww = 0; ww < nwarp_rows; ++ww) sum += sm.red[(size_t)ww * 2 * 6 * 32 + (q * 6 + c) * 32 + il];
+                    for (int ww = 0; ww < PS_W; ++ww) sum += sm.red[(size_t)ww * 2 * 6 * 32 + (q * 6 + c) * 32 + il];
                     a.part[((size_t)(kb + kloc) * 6 + c) * a.gpad + cta] = sum;
                 }
             }
@@ -361,9 +365,9 @@ k_persist_steps(const PersistArgs a)
                 const uint32_t xs = a.xseq0 + steps + 1;   // never 0
                 const uint32_t par = xs & 1u;
                 const size_t slot = (((size_t)par * a.world + a.rank) * a.nact_max + k);
-                if (lane < 6 * a.world)
+                for (int idx = lane; idx < 6 * a.world; idx += 32)
                 {
-                    const int r = lane / 6, c = lane % 6;
+                    const int r = idx / 6, c = idx % 6;
                     double v = f[0];
 #pragma unroll
                     for (int cc = 1; cc < 6; ++cc) if (c == cc) v = f[cc];
@@ -432,8 +436,9 @@ k_persist_steps(const PersistArgs a)
             const uint32_t per = ((len + PS_W - 1) / PS_W + 31) / 32 * 32;
             const uint32_t b = min(s0 + w * per, s1), e = min(b + per, s1);
             uint32_t cntw = 0;
-            for (uint32_t i = b + lane; i < e + 31 - ((e - b + 31) % 32 == 31 ? 0 : 0) && i - lane < e; i += 32)
+            for (uint32_t base = b; base < e; base += 32)
             {
+                const uint32_t i = base + lane;
                 const bool on = i < e && fabs(sub(itime, add(ldc(s.t + i), ldc(s.dt + i)))) < DBL_EPS2;
                 cntw += __popc(__ballot_sync(0xffffffffu, on));
             }
@@ -443,8 +448,9 @@ k_persist_steps(const PersistArgs a)
 #pragma unroll
             for (int ww = 0; ww < PS_W; ++ww) { if (ww < w) off += sm.wcnt[ww]; tot += sm.wcnt[ww]; }
             uint32_t *list = a.cta_list + (size_t)cta * a.slice;
-            for (uint32_t i = b + lane; i - lane < e; i += 32)
+            for (uint32_t base = b; base < e; base += 32)
             {
+                const uint32_t i = base + lane;
                 const bool on = i < e && fabs(sub(itime, add(ldc(s.t + i), ldc(s.dt + i)))) < DBL_EPS2;
                 const uint32_t bal = __ballot_sync(0xffffffffu, on);
                 if (on) list[off + __popc(bal & ((1u << lane) - 1u))] = i;

@@ -74,6 +74,15 @@ __global__ void k_predict(State s, uint32_t begin, uint32_t end, double itime,
     store_pred(s, i, predict_one(s, i, itime));
 }
 
+// Predicted set of the particles that were NOT corrected at `itime` (t != itime): used after the
+// persistent small-step kernel, which predicts in registers and stores only the active particles.
+__global__ void k_predict_rest(State s, uint32_t n, double itime)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n || s.t[i] == itime) return;
+    store_pred(s, i, predict_one(s, i, itime));
+}
+
 // init: predicted = current (reference: Hermite4::init_data, src/include/Hermite4.cpp:198-210)
 __global__ void k_copy_to_pred(State s, uint32_t n)
 {

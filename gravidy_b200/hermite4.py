@@ -212,6 +212,16 @@ class Hermite4B200:
     def set_tuning(self, variant=-1, jsplit=-1):
         self._ck(self.lib.gdy_set_tuning(self.h, variant, jsplit))
 
+    def set_persist(self, nact_max=-1):
+        """Active sets up to nact_max are stepped by the persistent kernel inside run() (0 = off)."""
+        self._ck(self.lib.gdy_set_persist(self.h, nact_max))
+
+    def persist_stats(self):
+        """(launches, block steps) done by the persistent small-step kernel so far."""
+        a, b = C.c_uint64(), C.c_uint64()
+        self._ck(self.lib.gdy_persist_stats(self.h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
     def measure_fp64_peak(self):
         tf, mhz = C.c_double(), C.c_double()
         self._ck(self.lib.gdy_measure_fp64_peak(self.h, C.byref(tf), C.byref(mhz)))

@@ -167,6 +167,14 @@ int gdy_force_sweep_full(gdy_ctx *ctx, int reps, float *ms_out);
 /* Force-kernel variant override for tuning (-1 = heuristic). */
 int gdy_set_tuning(gdy_ctx *ctx, int variant, int jsplit);
 
+/* Small active sets (nact <= nact_max) are stepped by ONE persistent cooperative kernel per run of
+ * consecutive small blocks inside gdy_run: predictor fused into the force evaluation, corrector and
+ * scheduler behind grid barriers, no host round trip per block step (replaces, for those steps, the
+ * per-step launch sequence of the reference: src/include/gpu/Hermite4GPU_integration.cpp:81-124).
+ * nact_max: 0 = off, < 0 = default (64), at most 512.  Sharded contexts need gdy_peer_attach first. */
+int gdy_set_persist(gdy_ctx *ctx, int nact_max);
+int gdy_persist_stats(const gdy_ctx *ctx, uint64_t *launches_out, uint64_t *steps_out);
+
 /* Measured denominators for the roofline (measurement infrastructure, not the hot path):
  * dependent-free DFMA loop on every SM -> TFLOP/s (2 flop per DFMA), and a device copy -> GB/s. */
 int gdy_measure_fp64_peak(gdy_ctx *ctx, double *tflops_out, double *sm_mhz_out);
