@@ -187,6 +187,12 @@ def run_b200(args, m, r, v):
 
     n = len(m)
     h = Hermite4B200(m, r, v, softening=1e-4, eta=0.01, device=local, rank=rank, world=world, nccl_uid=uid)
+    if world > 1:
+        # peer memory for the fused NVLink exchange of the persistent small-block kernel
+        hs = [None] * world
+        dist.all_gather_object(hs, h.peer_export())
+        h.peer_attach(hs)
+        dist.barrier()
     h.init_acc_jrk()
     h.sync()
     peak_tf, peak_mhz = h.measure_fp64_peak()
@@ -296,6 +302,7 @@ def run_b200(args, m, r, v):
             "integration": integ, "cpu_baseline": cpu, "wall_timed_s": wall_timed,
         }
         print(json.dumps(line), flush=True)
+    barrier()
     h.close()
     if world > 1:
         dist.destroy_process_group()

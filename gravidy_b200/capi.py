@@ -18,6 +18,7 @@ _ctx = C.c_void_p
 
 GDY_OK, GDY_ERR_INVALID, GDY_ERR_NO_DEVICE, GDY_ERR_CUDA, GDY_ERR_NCCL, GDY_ERR_STATE = 0, -1, -2, -3, -4, -5
 NCCL_UID_BYTES = 128
+PEER_HANDLE_BYTES = 128
 
 
 class RunStats(C.Structure):
@@ -68,6 +69,9 @@ SIGNATURES = {
     "gdy_set_tuning": (C.c_int, [_ctx, C.c_int, C.c_int]),
     "gdy_set_persist": (C.c_int, [_ctx, C.c_int]),
     "gdy_persist_stats": (C.c_int, [_ctx, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
+    "gdy_peer_export": (C.c_int, [_ctx, C.POINTER(C.c_uint8)]),
+    "gdy_peer_attach": (C.c_int, [_ctx, C.POINTER(C.c_uint8)]),
+    "gdy_persist_profile": (C.c_int, [_ctx, C.POINTER(C.c_uint64)]),
     "gdy_measure_fp64_peak": (C.c_int, [_ctx, _dp, _dp]),
     "gdy_measure_copy_bw": (C.c_int, [_ctx, _dp]),
     "gdy_launch_count": (C.c_uint64, [_ctx]),

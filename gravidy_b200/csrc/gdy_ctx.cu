@@ -18,6 +18,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <dlfcn.h>
+#include <unistd.h>
 #include <nccl.h>   // types only; the library is bound with dlopen so that a process which already
                     // carries an NCCL (e.g. torch's bundled one) shares it instead of loading a second.
 #include <vector>
@@ -107,18 +108,20 @@ struct gdy_ctx
     // persistent small-step kernel (gdy_persist.cuh)
     uint32_t ps_nact_max = 0;        // 0 = off
     uint32_t ps_grid = 0, ps_slice = 0, ps_gpad = 0;
-    double *ps_part = nullptr, *ps_cta_min = nullptr, *ps_act_next = nullptr;
-    uint32_t *ps_cta_cnt = nullptr, *ps_cta_list = nullptr, *ps_bar = nullptr;
+    uint4 *ps_part = nullptr;
+    double *ps_cta_min = nullptr, *ps_act_next = nullptr;
+    uint32_t *ps_cta_cnt = nullptr, *ps_cta_list = nullptr, *ps_flags = nullptr, *ps_exit_cnt = nullptr;
+    unsigned long long *ps_prof = nullptr;
     PersistCtl *ps_ctl = nullptr, *ps_ctl_host = nullptr;
-    TraceRec *ps_trace = nullptr, *ps_trace_host = nullptr;
+    TraceRec *ps_trace_host = nullptr;
+    uint32_t ps_epoch = 0;
     uint32_t ps_seq = 0, ps_xseq = 0;
     bool ps_last = false;            // the last block step was done by the persistent kernel
     // peer-memory exchange of the persistent path (world > 1)
     bool peers_ok = false;
-    double *xbuf = nullptr;          // my exchange buffer: slots then flags
-    double *xslot[PS_MAX_WORLD] = {};
-    uint32_t *xflag[PS_MAX_WORLD] = {};
-    void *xopened[PS_MAX_WORLD] = {};
+    uint4 *xbuf = nullptr;           // my exchange buffer (peers store into it)
+    uint4 *xslot[PS_MAX_WORLD] = {}; // every rank's buffer as seen from this device
+    void *xopened[PS_MAX_WORLD] = {};// mappings opened with cudaIpcOpenMemHandle (other processes)
     uint64_t ps_steps_total = 0, ps_launches = 0;
     char err[512] = "";
 };
@@ -197,7 +200,7 @@ namespace {
 
 constexpr size_t PART_MIN_DOUBLES = (size_t)8 << 20;   // 64 MiB of j-split partials at least
 constexpr uint32_t PS_STEPS_MAX = 4096;                // block steps per persistent launch
-constexpr uint32_t PS_DEFAULT_NACT = 64;               // active sets up to this size go to the persistent kernel
+constexpr uint32_t PS_DEFAULT_NACT = 512;              // active sets up to this size go to the persistent kernel
 
 int alloc_all(gdy_ctx *c)
 {
@@ -264,16 +267,23 @@ int alloc_all(gdy_ctx *c)
         CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, (const void *)k_persist_steps<false>, PS_T, sizeof(PersistSmem)));
         c->ps_grid = (uint32_t)c->num_sms;
         if (c->ps_grid > (uint32_t)PS_GMAX) c->ps_grid = PS_GMAX;
-        c->ps_slice = cdiv(c->n, c->ps_grid);
+        c->ps_slice = round_up(cdiv(c->n, c->ps_grid), 2);   // even: the list heads are read as uint2
         c->ps_gpad = round_up(c->ps_grid, 32);
-        CU(cudaMalloc(&c->ps_part, (size_t)PS_NACT_CAP * 6 * c->ps_gpad * sizeof(double)));
-        CU(cudaMalloc(&c->ps_cta_min, c->ps_grid * sizeof(double)));
+        CU(cudaMalloc(&c->ps_part, (size_t)PS_NACT_CAP * 6 * c->ps_gpad * sizeof(uint4)));
+        CU(cudaMemsetAsync(c->ps_part, 0, (size_t)PS_NACT_CAP * 6 * c->ps_gpad * sizeof(uint4), c->st));
+        CU(cudaMalloc(&c->ps_cta_min, 2 * c->ps_grid * sizeof(double)));
         CU(cudaMalloc(&c->ps_act_next, PS_NACT_CAP * sizeof(double)));
-        CU(cudaMalloc(&c->ps_cta_cnt, c->ps_grid * sizeof(uint32_t)));
-        CU(cudaMalloc(&c->ps_cta_list, (size_t)c->ps_grid * c->ps_slice * sizeof(uint32_t)));
-        CU(cudaMalloc(&c->ps_bar, 128));
+        CU(cudaMalloc(&c->ps_cta_cnt, 2 * c->ps_grid * sizeof(uint32_t)));
+        CU(cudaMalloc(&c->ps_cta_list, (size_t)2 * c->ps_grid * c->ps_slice * sizeof(uint32_t)));
+        CU(cudaMalloc(&c->ps_exit_cnt, c->ps_grid * sizeof(uint32_t)));
+        CU(cudaMalloc(&c->ps_flags, c->ps_grid * sizeof(uint32_t)));
+        CU(cudaMemsetAsync(c->ps_flags, 0, c->ps_grid * sizeof(uint32_t), c->st));
+        if (getenv("GDY_PERSIST_PROF"))
+        {
+            CU(cudaMalloc(&c->ps_prof, PS_NPROF * sizeof(unsigned long long)));
+            CU(cudaMemsetAsync(c->ps_prof, 0, PS_NPROF * sizeof(unsigned long long), c->st));
+        }
         CU(cudaMalloc(&c->ps_ctl, sizeof(PersistCtl)));
-        CU(cudaMalloc(&c->ps_trace, PS_STEPS_MAX * sizeof(TraceRec)));
         CU(cudaHostAlloc(&c->ps_ctl_host, sizeof(PersistCtl), cudaHostAllocDefault));
         CU(cudaHostAlloc(&c->ps_trace_host, PS_STEPS_MAX * sizeof(TraceRec), cudaHostAllocDefault));
         memset(c->ps_ctl_host, 0, sizeof(PersistCtl));
@@ -378,7 +388,11 @@ extern "C" int gdy_destroy(gdy_ctx *c)
     cudaFree(c->d_block_min); cudaFree(c->d_sched); cudaFree(c->d_atime); cudaFree(c->d_energy);
     cudaFree(c->d_stage); cudaFree(c->d_counter);
     cudaFree(c->ps_part); cudaFree(c->ps_cta_min); cudaFree(c->ps_act_next); cudaFree(c->ps_cta_cnt);
-    cudaFree(c->ps_cta_list); cudaFree(c->ps_bar); cudaFree(c->ps_ctl); cudaFree(c->ps_trace);
+    cudaFree(c->ps_cta_list); cudaFree(c->ps_flags); cudaFree(c->ps_exit_cnt); cudaFree(c->ps_ctl);
+    cudaFree(c->ps_prof);
+    for (int r = 0; r < PS_MAX_WORLD; ++r)
+        if (c->xopened[r]) cudaIpcCloseMemHandle(c->xopened[r]);
+    cudaFree(c->xbuf);
     if (c->ps_ctl_host) cudaFreeHost(c->ps_ctl_host);
     if (c->ps_trace_host) cudaFreeHost(c->ps_trace_host);
     if (c->pin) cudaFreeHost(c->pin);
@@ -862,12 +876,13 @@ int run_persist(gdy_ctx *c, double itime, uint32_t nact, double t_stop, uint32_t
     a.nact_max = c->ps_nact_max;
     a.slice = c->ps_slice; a.seq = ++c->ps_seq;
     a.part = c->ps_part; a.gpad = c->ps_gpad; a.cta_min = c->ps_cta_min; a.cta_cnt = c->ps_cta_cnt;
-    a.cta_list = c->ps_cta_list; a.act_next = c->ps_act_next; a.bar = c->ps_bar;
-    a.ctl_dev = c->ps_ctl; a.ctl_host = c->ps_ctl_host; a.trace = c->ps_trace;
+    a.cta_list = c->ps_cta_list; a.act_next = c->ps_act_next; a.flags = c->ps_flags; a.exit_cnt = c->ps_exit_cnt;
+    a.prof = c->ps_prof;
+    a.ctl_dev = c->ps_ctl; a.ctl_host = c->ps_ctl_host; a.trace = c->ps_trace_host;
+    a.epoch0 = c->ps_epoch;
     a.rank = c->rank; a.world = c->peers_ok ? c->world : 1;
     a.xseq0 = c->ps_xseq;
-    for (int r = 0; r < PS_MAX_WORLD; ++r) { a.xslot[r] = c->xslot[r]; a.xflag[r] = c->xflag[r]; }
-    CU(cudaMemsetAsync(c->ps_bar, 0, sizeof(uint32_t), c->st));
+    for (int r = 0; r < PS_MAX_WORLD; ++r) a.xslot[r] = c->xslot[r];
     if (timed) CU(cudaEventRecord(c->ev0, c->st));
     void *args[] = {&a};
     const void *fn = c->mask_self ? (const void *)k_persist_steps<true> : (const void *)k_persist_steps<false>;
@@ -876,6 +891,7 @@ int run_persist(gdy_ctx *c, double itime, uint32_t nact, double t_stop, uint32_t
     if (timed) CU(cudaEventRecord(c->ev1, c->st));
     CU(cudaStreamSynchronize(c->st));
     if (c->ps_ctl_host->seq != a.seq) return fail(c, GDY_ERR_STATE, "persistent kernel left no result (seq %u != %u)", c->ps_ctl_host->seq, a.seq);
+    c->ps_epoch = c->ps_ctl_host->epoch_end;
     c->ps_xseq += c->ps_ctl_host->steps;
     c->ps_steps_total += c->ps_ctl_host->steps;
     if (ms_out)
@@ -895,6 +911,92 @@ extern "C" int gdy_set_persist(gdy_ctx *c, int nact_max)
     if (c->world > 1 && !c->peers_ok && nact_max != 0)
         return fail(c, GDY_ERR_STATE, "a sharded context needs gdy_peer_attach before the persistent path");
     c->ps_nact_max = nact_max < 0 ? PS_DEFAULT_NACT : (uint32_t)nact_max;
+    return GDY_OK;
+}
+
+// ---- peer memory for the fused exchange of the persistent path ------------------------------------------------
+namespace {
+constexpr size_t XBUF_SLOTS = (size_t)2 * PS_MAX_WORLD * PS_NACT_CAP * 6;
+struct PeerHandle   // GDY_PEER_HANDLE_BYTES
+{
+    uint64_t magic;
+    int32_t pid, device, rank, world;
+    uint64_t ptr;
+    cudaIpcMemHandle_t ipc;
+    uint8_t pad[GDY_PEER_HANDLE_BYTES - 8 - 16 - 8 - sizeof(cudaIpcMemHandle_t)];
+};
+static_assert(sizeof(PeerHandle) == GDY_PEER_HANDLE_BYTES, "peer handle size");
+constexpr uint64_t PEER_MAGIC = 0x4744595f50454552ull;   // "GDY_PEER"
+}  // namespace
+
+extern "C" int gdy_peer_export(gdy_ctx *c, uint8_t *handle_out)
+{
+    if (!c || !handle_out) return GDY_ERR_INVALID;
+    BIND(c);
+    if (!c->xbuf)
+    {
+        CU(cudaMalloc(&c->xbuf, XBUF_SLOTS * sizeof(uint4)));
+        CU(cudaMemset(c->xbuf, 0, XBUF_SLOTS * sizeof(uint4)));
+    }
+    PeerHandle h{};
+    h.magic = PEER_MAGIC; h.pid = (int32_t)getpid(); h.device = c->device; h.rank = c->rank; h.world = c->world;
+    h.ptr = (uint64_t)(uintptr_t)c->xbuf;
+    CU(cudaIpcGetMemHandle(&h.ipc, c->xbuf));
+    memcpy(handle_out, &h, sizeof h);
+    return GDY_OK;
+}
+
+extern "C" int gdy_peer_attach(gdy_ctx *c, const uint8_t *handles)
+{
+    if (!c || !handles) return GDY_ERR_INVALID;
+    BIND(c);
+    if (c->world < 2) return GDY_OK;
+    if (c->world > PS_MAX_WORLD) return fail(c, GDY_ERR_INVALID, "world %d > %d", c->world, (int)PS_MAX_WORLD);
+    if (!c->xbuf) return fail(c, GDY_ERR_STATE, "gdy_peer_attach before gdy_peer_export");
+    for (int r = 0; r < c->world; ++r)
+    {
+        PeerHandle h;
+        memcpy(&h, handles + (size_t)r * GDY_PEER_HANDLE_BYTES, sizeof h);
+        if (h.magic != PEER_MAGIC || h.rank != r || h.world != c->world)
+            return fail(c, GDY_ERR_INVALID, "peer handle %d is not rank %d of %d", r, r, c->world);
+        if (r == c->rank) { c->xslot[r] = c->xbuf; continue; }
+        if (h.pid == (int32_t)getpid())
+        {
+            // same process (one thread per GPU): plain peer access to the other context's allocation
+            int can = 0;
+            CU(cudaDeviceCanAccessPeer(&can, c->device, h.device));
+            if (!can) return fail(c, GDY_ERR_CUDA, "device %d cannot access device %d", c->device, h.device);
+            cudaError_t e = cudaDeviceEnablePeerAccess(h.device, 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled)
+                return fail(c, GDY_ERR_CUDA, "cudaDeviceEnablePeerAccess(%d): %s", h.device, cudaGetErrorString(e));
+            (void)cudaGetLastError();
+            c->xslot[r] = (uint4 *)(uintptr_t)h.ptr;
+        }
+        else
+        {
+            void *p = nullptr;
+            CU(cudaIpcOpenMemHandle(&p, h.ipc, cudaIpcMemLazyEnablePeerAccess));
+            c->xopened[r] = p;
+            c->xslot[r] = (uint4 *)p;
+        }
+    }
+    c->peers_ok = true;
+    uint32_t def = PS_DEFAULT_NACT;
+    if (const char *e = getenv("GDY_PERSIST_NACT")) def = (uint32_t)atoi(e);
+    if (def > (uint32_t)PS_NACT_CAP) def = PS_NACT_CAP;
+    c->ps_nact_max = def;
+    return GDY_OK;
+}
+
+// ns spent per phase of the persistent kernel by CTA 0 (only with GDY_PERSIST_PROF=1 in the environment)
+extern "C" int gdy_persist_profile(gdy_ctx *c, uint64_t *ns_out /* [PS_NPROF = 144] */)
+{
+    if (!c || !ns_out) return GDY_ERR_INVALID;
+    BIND(c);
+    memset(ns_out, 0, PS_NPROF * sizeof(uint64_t));
+    if (!c->ps_prof) return GDY_OK;
+    CU(cudaMemcpyAsync(ns_out, c->ps_prof, PS_NPROF * sizeof(uint64_t), cudaMemcpyDeviceToHost, c->st));
+    CU(cudaStreamSynchronize(c->st));
     return GDY_OK;
 }
 
@@ -948,16 +1050,18 @@ extern "C" int gdy_run(gdy_ctx *c, double atime, double itime0, double t_stop, u
             if (it < trace_cap && (trace_nact || trace_itime || trace_us))
             {
                 const uint64_t k = pc.steps < trace_cap - it ? pc.steps : trace_cap - it;
-                CU(cudaMemcpyAsync(c->ps_trace_host, c->ps_trace, k * sizeof(TraceRec), cudaMemcpyDeviceToHost, c->st));
-                CU(cudaStreamSynchronize(c->st));
                 const auto now = std::chrono::steady_clock::now();
-                const float us = std::chrono::duration<float, std::micro>(now - tick).count() / (float)pc.steps;
+                const float us = std::chrono::duration<float, std::micro>(now - tick).count();
                 tick = now;
+                // per-step time = the kernel's own stamps; what the launch cost around them goes to its first step
+                const float in_kernel = c->ps_trace_host[k - 1].ns * 1e-3f;
                 for (uint64_t q = 0; q < k; ++q)
                 {
                     if (trace_nact) trace_nact[it + q] = c->ps_trace_host[q].nact;
                     if (trace_itime) trace_itime[it + q] = c->ps_trace_host[q].itime;
-                    if (trace_us) trace_us[it + q] = us;
+                    if (trace_us)
+                        trace_us[it + q] = q ? (c->ps_trace_host[q].ns - c->ps_trace_host[q - 1].ns) * 1e-3f
+                                             : c->ps_trace_host[0].ns * 1e-3f + (k == pc.steps && us > in_kernel ? us - in_kernel : 0.f);
                 }
             }
             else tick = std::chrono::steady_clock::now();
@@ -967,7 +1071,7 @@ extern "C" int gdy_run(gdy_ctx *c, double atime, double itime0, double t_stop, u
             c->pin->sched.nact = pc.nact_next;
             c->pin->sched.itime = pc.atime;
             c->ps_last = true;
-            if (pc.steps >= budget && ITIME < t_stop && !(max_steps && it >= max_steps))
+            if (!pc.move_is_next && ITIME < t_stop && !(max_steps && it >= max_steps))
             {
                 // stopped on the per-launch step cap: State.move still holds the last completed step's list
                 if ((r = launch_sched(c, ATIME, false))) return r;

@@ -171,7 +171,20 @@ __device__ __forceinline__ double correct_core(const State &s, uint32_t i, doubl
     const double dt3 = mul(dt2, dt1);
     const double dt4 = mul(dt2, dt2);
     const double dt5 = mul(dt4, dt1);
-    const double c4_24 = dvd(dt4, 24.0), c5_120 = dvd(dt5, 120.0), c3_6 = dvd(dt3, 6.0);
+    // Every step the scheduler hands out is a power of two (init_dt: pow(2, k); normalize_dt: old/8, old/4,
+    // old/2, old, 2*old, 2^-23, 2^-3).  Dividing BY a power of two, or a power of two by a constant, is an
+    // exact scaling of a correctly rounded constant, so the six divisions below are done as multiplications
+    // with bit-identical results (no subnormals: dt >= 2^-23); anything else takes the true divisions.
+    const bool pow2 = (__double_as_longlong(dt1) & 0x000fffffffffffffLL) == 0 && dt1 >= D_TIME_MIN && dt1 <= 1.0;
+    double c4_24, c5_120, c3_6, inv_dt2 = 0.0, inv_dt3 = 0.0;
+    if (pow2)
+    {
+        c4_24 = mul(dt4, dvd(1.0, 24.0)); c5_120 = mul(dt5, dvd(1.0, 120.0)); c3_6 = mul(dt3, dvd(1.0, 6.0));
+        // 1/dt2, 1/dt3 by exponent arithmetic: dt^k = 2^e  ->  bits(2^-e) = (2046 << 52) - bits(2^e)
+        inv_dt2 = __longlong_as_double((2046LL << 52) - __double_as_longlong(dt2));
+        inv_dt3 = __longlong_as_double((2046LL << 52) - __double_as_longlong(dt3));
+    }
+    else { c4_24 = dvd(dt4, 24.0); c5_120 = dvd(dt5, 120.0); c3_6 = dvd(dt3, 6.0); }
 
     double a2[3], a3[3];
 #pragma unroll
@@ -179,9 +192,11 @@ __device__ __forceinline__ double correct_core(const State &s, uint32_t i, doubl
     {
         const double d = sub(q.oa[c], q.fa[c]);
         // (-6*(old.a - f.a) - dt1*(4*old.a1 + 2*f.a1)) / dt2
-        a2[c] = dvd(sub(mul(-6.0, d), mul(dt1, add(mul(4.0, q.oj[c]), mul(2.0, q.fj[c])))), dt2);
+        const double n2 = sub(mul(-6.0, d), mul(dt1, add(mul(4.0, q.oj[c]), mul(2.0, q.fj[c]))));
         // (12*(old.a - f.a) + 6*dt1*(old.a1 + f.a1)) / dt3
-        a3[c] = dvd(add(mul(12.0, d), mul(mul(6.0, dt1), add(q.oj[c], q.fj[c]))), dt3);
+        const double n3 = add(mul(12.0, d), mul(mul(6.0, dt1), add(q.oj[c], q.fj[c])));
+        a2[c] = pow2 ? mul(n2, inv_dt2) : dvd(n2, dt2);
+        a3[c] = pow2 ? mul(n3, inv_dt3) : dvd(n3, dt3);
         s.a2[c][i] = a2[c];
         s.a3[c][i] = a3[c];
     }
@@ -241,25 +256,6 @@ __global__ void k_correct(State s, uint32_t nact, double itime, double eta,
     const double *pp = s.pb + pbidx(i, 0);
     q.p = Pred6{pp[0], pp[JB], pp[2 * JB], pp[3 * JB], pp[4 * JB], pp[5 * JB]};
     correct_core(s, i, itime, eta, q);
-}
-
-// Persistent-kernel flavour: the forces being replaced are read past L1 (another SM may have written
-// them a few steps ago), the new ones come in registers; save-old and the force store are fused in.
-__device__ __forceinline__ double correct_one(const State &s, uint32_t i, double itime, double eta,
-                                              const Pred6 &p, const double *f /* [6] */)
-{
-    CorrIn q;
-    q.dt1 = __ldcg(s.dt + i);
-#pragma unroll
-    for (int c = 0; c < 3; ++c)
-    {
-        q.oa[c] = __ldcg(s.f[c] + i); q.oj[c] = __ldcg(s.f[3 + c] + i);
-        s.old[c][i] = q.oa[c]; s.old[3 + c][i] = q.oj[c];
-        q.fa[c] = f[c]; q.fj[c] = f[3 + c];
-        s.f[c][i] = f[c]; s.f[3 + c][i] = f[3 + c];
-    }
-    q.p = p;
-    return correct_core(s, i, itime, eta, q);
 }
 
 // ---- scheduler -----------------------------------------------------------------------------------

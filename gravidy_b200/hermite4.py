@@ -212,6 +212,18 @@ class Hermite4B200:
     def set_tuning(self, variant=-1, jsplit=-1):
         self._ck(self.lib.gdy_set_tuning(self.h, variant, jsplit))
 
+    def peer_export(self) -> bytes:
+        """Handle of this shard's exchange buffer (for the fused NVLink exchange of the persistent path)."""
+        buf = (C.c_uint8 * capi.PEER_HANDLE_BYTES)()
+        self._ck(self.lib.gdy_peer_export(self.h, buf))
+        return bytes(buf)
+
+    def peer_attach(self, handles):
+        """handles: the world's peer_export() results in rank order."""
+        blob = b"".join(handles)
+        buf = (C.c_uint8 * len(blob)).from_buffer_copy(blob)
+        self._ck(self.lib.gdy_peer_attach(self.h, buf))
+
     def set_persist(self, nact_max=-1):
         """Active sets up to nact_max are stepped by the persistent kernel inside run() (0 = off)."""
         self._ck(self.lib.gdy_set_persist(self.h, nact_max))
@@ -221,6 +233,12 @@ class Hermite4B200:
         a, b = C.c_uint64(), C.c_uint64()
         self._ck(self.lib.gdy_persist_stats(self.h, C.byref(a), C.byref(b)))
         return a.value, b.value
+
+    def persist_profile(self):
+        """ns per phase of the persistent kernel (CTA 0); zeros unless GDY_PERSIST_PROF=1."""
+        out = (C.c_uint64 * 144)()
+        self._ck(self.lib.gdy_persist_profile(self.h, out))
+        return [int(x) for x in out]
 
     def measure_fp64_peak(self):
         tf, mhz = C.c_double(), C.c_double()

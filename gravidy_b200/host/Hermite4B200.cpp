@@ -61,6 +61,13 @@ Hermite4B200::Hermite4B200(NbodySystem *ns_, Logger *logger_, NbodyUtils *nu_) :
               "gdy_create_sharded");
         check(gdy_upload_particles(shards[g], &ns->h_r[0].x, &ns->h_v[0].x), g, "gdy_upload_particles");
     });
+    if (ngpus > 1)
+    {
+        // peer memory for the fused NVLink exchange of the persistent small-block kernel
+        std::vector<uint8_t> handles((size_t)ngpus * GDY_PEER_HANDLE_BYTES);
+        each_shard([&](int g) { check(gdy_peer_export(shards[g], &handles[(size_t)g * GDY_PEER_HANDLE_BYTES]), g, "gdy_peer_export"); });
+        each_shard([&](int g) { check(gdy_peer_attach(shards[g], handles.data()), g, "gdy_peer_attach"); });
+    }
     nu->neighbour_distance = [this](int k, std::vector<double> &out) {
         out.resize(ns->n);
         check(gdy_neighbour_distance(shards[0], k, out.data()), 0, "gdy_neighbour_distance");

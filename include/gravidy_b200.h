@@ -171,9 +171,25 @@ int gdy_set_tuning(gdy_ctx *ctx, int variant, int jsplit);
  * consecutive small blocks inside gdy_run: predictor fused into the force evaluation, corrector and
  * scheduler behind grid barriers, no host round trip per block step (replaces, for those steps, the
  * per-step launch sequence of the reference: src/include/gpu/Hermite4GPU_integration.cpp:81-124).
- * nact_max: 0 = off, < 0 = default (64), at most 512.  Sharded contexts need gdy_peer_attach first. */
+ * nact_max: 0 = off, < 0 = default (512), at most 2048.  Sharded contexts need gdy_peer_attach first. */
 int gdy_set_persist(gdy_ctx *ctx, int nact_max);
 int gdy_persist_stats(const gdy_ctx *ctx, uint64_t *launches_out, uint64_t *steps_out);
+/* ns per phase of that kernel seen by CTA 0 (P1a, P1b, barrier 1, P2, barrier 2, P3, exit, ...); all zero
+ * unless GDY_PERSIST_PROF=1 was in the environment at gdy_create (measurement aid). */
+int gdy_persist_profile(gdy_ctx *ctx, uint64_t *ns_out /* [144] */);
+
+/* Peer memory for the sharded persistent path.  With world > 1 the per-shard force sums of a small block
+ * are exchanged INSIDE the persistent kernel: every rank stores its sum as flagged 16-byte slots straight
+ * into every peer's buffer over NVLink and adds the world's sums in rank order (bit-identical on all
+ * ranks) — no NCCL call, no launch, no host (replaces the host-side sum over GPUs of the reference,
+ * src/include/gpu/Hermite4GPU.cu:512-530, for those steps; big blocks keep ncclAllReduce).
+ *   gdy_peer_export: handle of THIS context's exchange buffer (GDY_PEER_HANDLE_BYTES bytes);
+ *   gdy_peer_attach: all `world` handles in rank order, gathered by the caller (MPI, torch.distributed,
+ *                    a vector in the one-process-many-threads host program).  Same process: peer access;
+ *                    other processes: CUDA IPC.  Switches the persistent path on for this shard. */
+#define GDY_PEER_HANDLE_BYTES 128
+int gdy_peer_export(gdy_ctx *ctx, uint8_t *handle_out);
+int gdy_peer_attach(gdy_ctx *ctx, const uint8_t *handles);
 
 /* Measured denominators for the roofline (measurement infrastructure, not the hot path):
  * dependent-free DFMA loop on every SM -> TFLOP/s (2 flop per DFMA), and a device copy -> GB/s. */

@@ -172,7 +172,7 @@ def _rel_rows(a, b):
     return (np.linalg.norm(a - b, axis=1) / np.maximum(np.linalg.norm(b, axis=1), 1e-300)).max()
 
 
-@pytest.mark.parametrize("persist", [0, -1, 2, 512])
+@pytest.mark.parametrize("persist", [0, -1, 2, 64])
 @pytest.mark.parametrize("name", STEP_FIXTURES)
 def test_fused_run_equals_hook_loop(H, golden_dir, name, persist):
     """gdy_run == the hook sequence.  persist = 0: per-hook kernels with the chained scheduler and the
@@ -195,7 +195,7 @@ def test_fused_run_equals_hook_loop(H, golden_dir, name, persist):
     if persist == 0:
         assert steps == 0
     else:
-        lim = 64 if persist < 0 else persist
+        lim = 512 if persist < 0 else persist
         assert steps == int((g["nact"] <= lim).sum()) and launches >= 1
     a = h.get_state()
     h2 = H(g["m"], g["r"], g["v"], softening=float(g["softening"]), eta=float(g["eta"]))

@@ -56,8 +56,11 @@ def _two_gpu_available():
 
 
 @pytest.mark.skipif(not _two_gpu_available(), reason="needs 2 GPUs")
-def test_two_real_shards_nccl(H):
-    n, nsteps = 3000, 60
+@pytest.mark.parametrize("peers", [False, True])
+def test_two_real_shards_nccl(H, peers):
+    """peers = False: every block step through the per-hook kernels + ncclAllReduce.  peers = True: small
+    blocks through the persistent kernel with the fused NVLink exchange (peer memory), big ones as before."""
+    n, nsteps = 3000, 300 if peers else 60
     m, r, v = plummer(n, seed=8)
     single = H(m, r, v)
     single.init_acc_jrk()
@@ -67,15 +70,24 @@ def test_two_real_shards_nccl(H):
 
     uid = H.nccl_unique_id()
     out, err = [None, None], []
+    handles = [None, None]
+    gate = threading.Barrier(2)
 
     def work(rank):
         try:
             h = H(m, r, v, device=rank, rank=rank, world=2, nccl_uid=uid)
+            if peers:
+                handles[rank] = h.peer_export()
+                gate.wait(timeout=120)
+                h.peer_attach(handles)
+                gate.wait(timeout=120)
             h.init_acc_jrk()
             f0 = h.download_forces()
             at = h.init_dt(0.0)
             st, tn, ti = h.run(at, 1e9, max_steps=nsteps, trace_cap=nsteps)
-            out[rank] = (f0, at, st.atime, tn, ti, h.get_state())
+            out[rank] = (f0, at, st.atime, tn, ti, h.get_state(), h.persist_stats())
+            if peers:
+                gate.wait(timeout=120)   # nobody unmaps its buffer while a peer may still store into it
             h.close()
         except Exception as e:   # noqa: BLE001
             err.append(e)
@@ -99,6 +111,10 @@ def test_two_real_shards_nccl(H):
     for rank in range(2):
         lo, hi = H.shard_range(n, rank, 2)
         assert np.array_equal(out[rank][5]["p7"][lo:hi, 6], s1["p7"][lo:hi, 6])
+    if peers:
+        assert a[6][1] > 0 and a[6] == b[6]                # the persistent kernel did steps, the same on both
+    else:
+        assert a[6][1] == 0
     # and follows the single-GPU run
     assert np.array_equal(a[3], tn1) and np.array_equal(a[4], ti1) and a[2] == st1.atime
     np.testing.assert_allclose(a[5]["r4"], s1["r4"], rtol=0, atol=1e-11)

@@ -24,8 +24,8 @@ EOF
 done
 
 echo "== integrations"
-timeout 300 python tools/integrate.py --n 16384 --t 1 --out $O/integrate_n16k.json > /dev/null 2> $O/integrate.err; echo "rc=$?"
-timeout 600 python tools/integrate.py --n 65536 --t 0.25 --spectrum salpeter --out $O/integrate_n64k_salpeter.json > /dev/null 2>> $O/integrate.err; echo "rc=$?"
+timeout 300 python tools/integrate.py --particles 16384 --tend 1 --out $O/integrate_n16k.json > /dev/null 2> $O/integrate.err; echo "rc=$?"
+timeout 600 python tools/integrate.py --particles 65536 --tend 0.25 --spectrum salpeter --out $O/integrate_n64k_salpeter.json > /dev/null 2>> $O/integrate.err; echo "rc=$?"
 python tools/step_latency.py --n 262144 --steps 1500 > $O/step_latency_n256k.txt 2>&1
 python tools/step_latency.py --n 16384 --steps 3000 > $O/step_latency_n16k.txt 2>&1
 
@@ -41,7 +41,7 @@ timeout 900 ncu --set full --clock-control none --import-source on -k 'regex:k_p
   python bench.py --steps 1 --warmup 3 --no-cpu-baseline --integration-steps 60 > $O/ncu_step.log 2>&1; echo "rc=$?"
 
 echo "== full N=256k to t=1 (1 GPU)"
-timeout 900 python tools/integrate.py --n 262144 --t 1 --out $O/integrate_n256k_1gpu.json > /dev/null 2>> $O/integrate.err; echo "rc=$?"
+timeout 900 python tools/integrate.py --particles 262144 --tend 1 --out $O/integrate_n256k_1gpu.json > /dev/null 2>> $O/integrate.err; echo "rc=$?"
 python - <<EOF
 import json
 for f in ("integrate_n16k", "integrate_n64k_salpeter", "integrate_n256k_1gpu"):

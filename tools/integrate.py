@@ -6,8 +6,8 @@ Prints ONE JSON line: block steps, sum of nact, pairs, wall seconds of the `whil
 init_acc_jrk, the energy diagnostic and nbody_attributes are outside the window on both sides),
 GFLOP/s at 60 flop/pair, the energy error at the end, and the per-nact-bin step times.
 
-    python tools/integrate.py --n 16384 --t 1
-    python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 tools/integrate.py --n 262144 --t 1
+    python tools/integrate.py --particles 16384 --tend 1
+    python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 tools/integrate.py --particles 262144 --tend 1
 """
 import argparse
 import json
@@ -24,14 +24,15 @@ from gravidy_b200.plummer import plummer, default_seed  # noqa: E402
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--n", type=int, default=16384)
-    ap.add_argument("--t", type=float, default=1.0)
+    ap.add_argument("--particles", "-N", dest="n", type=int, default=16384)
+    ap.add_argument("--tend", "-T", dest="t", type=float, default=1.0)
     ap.add_argument("--spectrum", default="equal")
     ap.add_argument("--softening", type=float, default=1e-4)
     ap.add_argument("--eta", type=float, default=0.01)
     ap.add_argument("--max-steps", type=int, default=0)
     ap.add_argument("--trace", type=int, default=400000)
     ap.add_argument("--out", default="")
+    ap.add_argument("--no-peers", action="store_true", help="sharded run without the fused NVLink exchange")
     a = ap.parse_args()
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -54,6 +55,11 @@ def main():
     m, r, v = plummer(a.n, seed=default_seed(a.n), mass_spectrum=a.spectrum)
     h = Hermite4B200(m, r, v, softening=a.softening, eta=a.eta, device=local, rank=rank, world=world,
                      nccl_uid=uid)
+    if world > 1 and not a.no_peers:
+        hs = [None] * world
+        dist.all_gather_object(hs, h.peer_export())
+        h.peer_attach(hs)
+        dist.barrier()
     t0 = time.perf_counter()
     h.init_acc_jrk()
     h.sync()
@@ -91,12 +97,15 @@ def main():
         "e0": e0[0], "e1": e1[0], "cum_rel_energy_error": abs((e1[0] - e0[0]) / e0[0]),
         "init_acc_jrk_s": t_init, "energy_s": t_energy, "launches": h.launch_count(), "bins": bins,
     }
+    line["persist_launches"], line["persist_steps"] = h.persist_stats()
     if rank == 0:
         s = json.dumps(line)
         print(s, flush=True)
         if a.out:
             with open(a.out, "w") as f:
                 f.write(s + "\n")
+    if dist is not None:
+        dist.barrier()
     h.close()
     if dist is not None:
         dist.destroy_process_group()
