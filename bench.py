@@ -33,6 +33,7 @@ sys.path.insert(0, ROOT)
 FLOP_PER_PAIR = 60.0
 METRIC = "hermite_fp64_gflops_60flop_per_pair_N256k"
 UNIT = "GFLOP/s"
+NCU_DRAM_BYTES_PER_LAUNCH = 14909440 + 2216448   # profiles/r01_force_warp_ncu_v3.md
 
 
 def parse_args():
@@ -41,7 +42,7 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--n", type=int, default=262144, help="particles (BASELINE config: 256k)")
+    ap.add_argument("--n", "--particles", dest="n", type=int, default=262144, help="particles (BASELINE config: 256k)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-integration", action="store_true")
     ap.add_argument("--integration-steps", type=int, default=400)
@@ -291,7 +292,12 @@ def run_b200(args, m, r, v):
             "pairs_per_s": rate,
             "frac_fp64_peak": gflops / 1e3 / (peak_tf * world),
             "roofline": {"bound": "fp64", "achieved": kern_tf, "peak": peak_tf, "unit": "TFLOP/s",
-                         "frac": kern_tf / peak_tf, "traffic": None,
+                         "frac": kern_tf / peak_tf,
+                         "traffic": NCU_DRAM_BYTES_PER_LAUNCH if (n == 262144 and world == 1) else None,
+                         "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of one ncu --set full "
+                                           "capture of this kernel at N=262144 on 1 GPU "
+                                           "(profiles/r01_force_warp_ncu_v3.md): 14.91 MB + 2.22 MB; "
+                                           "algorithmic 14.7 MB in + 12.6 MB out",
                          "kernel": "k_force_warp<IPT=2,WI=4,WJ=1,NST=3>",
                          "peak_source": "DFMA micro-benchmark on this GPU (gdy_measure_fp64_peak); "
                                         "MEASURED_PEAKS.json has no FP64 entry",
