@@ -242,6 +242,8 @@ struct PersistSmem
     double si[6 * PS_ICH];            // predicted i-chunk
     double red[PS_W * 2 * 6 * 32];    // cross-warp fold
     double dmin[PS_W];
+    double smin[PS_W];                // P1a, long slices: per-warp minimum of t+dt and how many attain it
+    uint32_t scnt[PS_W];
     double fsum[2][6];                // P2: summed force of the two particles in flight
     uint32_t ilist[PS_NACT_CAP];      // active list of the current step
     uint32_t lista[PS_NACT_CAP];      // next: corrected particles that are due again
@@ -319,6 +321,79 @@ __device__ __forceinline__ unsigned long long gtimer()
     return t;
 }
 
+// Warp-level scan of the particles [b0, b1): the minimum of t+dt over those NOT due at itime, and the ordered
+// list of the particles that attain it (find_particles_to_move / next_integration_time of the next step,
+// reference: src/include/Hermite4.cpp:63-102, for one slice).  The first PS_SCAN_RW rounds of 32 stay in
+// registers; longer ranges are re-read for the list.
+constexpr int PS_SCAN_RW = 8;
+constexpr int PS_SCAN_SPLIT = 32;   // slices longer than this many rounds of 32 are scanned by all warps (measured:
+                                    // N = 64k, 14 rounds: one warp hidden behind the staging is faster; N = 256k, 56: split is)
+__device__ __forceinline__ void warp_scan_slice(const State &s, double itime, uint32_t b0, uint32_t b1, uint32_t *list,
+                                                double &m_out, uint32_t &cnt_out)
+{
+    constexpr int RW = PS_SCAN_RW;
+    const double INF = __longlong_as_double(0x7ff0000000000000LL);
+    const int lane = threadIdx.x & 31;
+    const uint32_t wr = (b1 - b0 + 31) / 32;
+    double tt[RW];
+#pragma unroll
+    for (int r = 0; r < RW; ++r)
+    {
+        const uint32_t i = b0 + r * 32 + lane;
+        tt[r] = i < b1 ? add(ldc(s.t + i), ldc(s.dt + i)) : INF;
+    }
+    double m = INF;
+#pragma unroll
+    for (int r = 0; r < RW; ++r) if (!due_at(itime, tt[r])) m = fmin(m, tt[r]);
+    for (uint32_t r0 = RW; r0 < wr; r0 += RW)
+    {
+        double t2[RW];
+#pragma unroll
+        for (int r = 0; r < RW; ++r)
+        {
+            const uint32_t i = b0 + (r0 + r) * 32 + lane;
+            t2[r] = i < b1 ? add(ldc(s.t + i), ldc(s.dt + i)) : INF;
+        }
+#pragma unroll
+        for (int r = 0; r < RW; ++r) if (!due_at(itime, t2[r])) m = fmin(m, t2[r]);
+    }
+#pragma unroll
+    for (int off = 16; off; off >>= 1) m = fmin(m, __shfl_xor_sync(0xffffffffu, m, off));
+    uint32_t running = 0;
+    if (m < INF)
+    {
+#pragma unroll
+        for (int r = 0; r < RW; ++r)
+            if ((uint32_t)r < wr)
+            {
+                const bool on = tt[r] == m && !due_at(itime, tt[r]);
+                const uint32_t bal = __ballot_sync(0xffffffffu, on);
+                if (on) list[running + __popc(bal & ((1u << lane) - 1u))] = b0 + r * 32 + lane;
+                running += __popc(bal);
+            }
+        for (uint32_t r0 = RW; r0 < wr; r0 += RW)
+        {
+            double t2[RW];
+#pragma unroll
+            for (int r = 0; r < RW; ++r)
+            {
+                const uint32_t i = b0 + (r0 + r) * 32 + lane;
+                t2[r] = i < b1 ? add(ldc(s.t + i), ldc(s.dt + i)) : INF;
+            }
+#pragma unroll
+            for (int r = 0; r < RW; ++r)
+            {
+                const bool on = t2[r] == m && !due_at(itime, t2[r]);
+                const uint32_t bal = __ballot_sync(0xffffffffu, on);
+                if (on) list[running + __popc(bal & ((1u << lane) - 1u))] = b0 + (r0 + r) * 32 + lane;
+                running += __popc(bal);
+            }
+        }
+    }
+    m_out = m;
+    cnt_out = running;
+}
+
 template <bool MASK>
 __global__ void __launch_bounds__(PS_T, 1)
 k_persist_steps(const PersistArgs a)
@@ -367,59 +442,58 @@ k_persist_steps(const PersistArgs a)
         const uint32_t par = steps & 1u;
         GDY_STAMP(1);
         // ---- P1a: slice minimum of t+dt over the non-active particles and who attains it ----------------------
-        // One warp does it alone, without CTA barriers, while the others already stage the j-slice.
-        if (w == PS_W - 1)
+        // Short slices (<= 1024 particles): one warp does it alone, without CTA barriers, while the others already
+        // stage the j-slice.  Longer slices (N > ~150k): every warp scans a contiguous sub-slice (one L2 latency
+        // instead of a chain of them), candidates go to the sub-slice's own offset of the list, and one warp
+        // closes the gaps of the sub-slices that attain the slice minimum.
         {
-            constexpr int RW = 8;   // rounds of 32 particles whose t+dt stay in registers
             const uint32_t wr = (s1 - s0 + 31) / 32;
-            double tt[RW];
-#pragma unroll
-            for (int r = 0; r < RW; ++r)
-            {
-                const uint32_t i = s0 + r * 32 + lane;
-                tt[r] = i < s1 ? add(ldc(s.t + i), ldc(s.dt + i)) : INF;
-            }
-            double m = INF;
-#pragma unroll
-            for (int r = 0; r < RW; ++r) if (!due_at(itime, tt[r])) m = fmin(m, tt[r]);
-            for (uint32_t r0 = RW; r0 < wr; r0 += RW)
-            {
-                double t2[RW];
-#pragma unroll
-                for (int r = 0; r < RW; ++r)
-                {
-                    const uint32_t i = s0 + (r0 + r) * 32 + lane;
-                    t2[r] = i < s1 ? add(ldc(s.t + i), ldc(s.dt + i)) : INF;
-                }
-#pragma unroll
-                for (int r = 0; r < RW; ++r) if (!due_at(itime, t2[r])) m = fmin(m, t2[r]);
-            }
-#pragma unroll
-            for (int off = 16; off; off >>= 1) m = fmin(m, __shfl_xor_sync(0xffffffffu, m, off));
             uint32_t *list = a.cta_list + ((size_t)par * G + cta) * a.slice;
-            uint32_t running = 0;
-            if (m < INF)
+            if (wr <= (uint32_t)PS_SCAN_SPLIT)
             {
-#pragma unroll
-                for (int r = 0; r < RW; ++r)
-                    if ((uint32_t)r < wr)
-                    {
-                        const bool on = tt[r] == m && !due_at(itime, tt[r]);
-                        const uint32_t bal = __ballot_sync(0xffffffffu, on);
-                        if (on) list[running + __popc(bal & ((1u << lane) - 1u))] = s0 + r * 32 + lane;
-                        running += __popc(bal);
-                    }
-                for (uint32_t r = RW; r < wr; ++r)
+                if (w == PS_W - 1)
                 {
-                    const uint32_t i = s0 + r * 32 + lane;
-                    const double t2 = i < s1 ? add(ldc(s.t + i), ldc(s.dt + i)) : INF;
-                    const bool on = t2 == m && !due_at(itime, t2);
-                    const uint32_t bal = __ballot_sync(0xffffffffu, on);
-                    if (on) list[running + __popc(bal & ((1u << lane) - 1u))] = i;
-                    running += __popc(bal);
+                    double m;
+                    uint32_t running;
+                    warp_scan_slice(s, itime, s0, s1, list, m, running);
+                    if (lane == 0) { a.cta_min[par * G + cta] = m; a.cta_cnt[par * G + cta] = running; }
                 }
             }
-            if (lane == 0) { a.cta_min[par * G + cta] = m; a.cta_cnt[par * G + cta] = running; }
+            else
+            {
+                const uint32_t per = ((wr + PS_W - 1) / PS_W) * 32;   // particles per warp
+                const uint32_t b0 = min(s0 + (uint32_t)w * per, s1), b1 = min(b0 + per, s1);
+                double m;
+                uint32_t running;
+                warp_scan_slice(s, itime, b0, b1, list + (b0 - s0), m, running);
+                if (lane == 0) { sm.smin[w] = m; sm.scnt[w] = running; }
+                __syncthreads();
+                if (w == PS_W - 1)
+                {
+                    double mm = sm.smin[0];
+#pragma unroll
+                    for (int ww = 1; ww < PS_W; ++ww) mm = fmin(mm, sm.smin[ww]);
+                    uint32_t tot = 0;
+                    if (mm < INF)
+                        for (int ww = 0; ww < PS_W; ++ww)
+                            if (sm.smin[ww] == mm)
+                            {
+                                const uint32_t c = sm.scnt[ww];
+                                const uint32_t so = min((uint32_t)ww * per, s1 - s0);
+                                if (so != tot)   // move down: writes never pass the reads (tot <= so)
+                                    for (uint32_t p0 = 0; p0 < c; p0 += 32)
+                                    {
+                                        const bool on = p0 + lane < c;
+                                        const uint32_t v = on ? __ldcg(list + so + p0 + lane) : 0u;
+                                        __syncwarp();
+                                        if (on) list[tot + p0 + lane] = v;
+                                        __syncwarp();
+                                    }
+                                tot += c;
+                            }
+                    if (lane == 0) { a.cta_min[par * G + cta] = mm; a.cta_cnt[par * G + cta] = tot; }
+                }
+            }
         }
         GDY_PROF(0);
         GDY_STAMP(4);
