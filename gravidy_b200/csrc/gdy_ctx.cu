@@ -1202,9 +1202,9 @@ extern "C" int gdy_measure_fp64_peak(gdy_ctx *c, double *tflops_out, double *sm_
     const int iters = 4096;                            // x 64 DFMA per thread
     double *out = c->s.part;                           // scratch (>= 8 Mi doubles)
     using Fn = void (*)(double *, int, double, double);
-    const Fn fns[3] = {k_dfma_peak<4>, k_dfma_peak<8>, k_dfma_peak<16>};
+    const Fn fns[5] = {k_dfma_peak<4>, k_dfma_peak<8>, k_dfma_peak<16>, k_dfma_peak_acc<8>, k_dfma_peak_acc<16>};
     double best_tf = 0.0;
-    for (int f = 0; f < 3; ++f)
+    for (int f = 0; f < 5; ++f)
         for (int per_sm = 1; per_sm <= 8; per_sm *= 2)  // 256..2048 resident threads per SM
         {
             const int blocks = c->num_sms * per_sm;

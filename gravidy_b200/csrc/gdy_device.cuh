@@ -118,8 +118,8 @@ __device__ __forceinline__ double rsqrt_f64(double a)
     const double t = a * y0;
     const double e = fma(-t, y0, 1.0);
     const double p = fma(0.375, e, 0.5);
-    const double q = y0 * e;
-    return fma(p, q, y0);
+    const double ep = e * p;
+    return fma(y0, ep, y0);   // two distinct register sources: a DFMA with three runs at 3/4 rate (tools/fp64_mix.cu)
 }
 
 // ---- the pair interaction -----------------------------------------------------------------------

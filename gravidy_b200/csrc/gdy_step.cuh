@@ -573,4 +573,29 @@ __global__ void __launch_bounds__(256) k_dfma_peak(double *out, int iters, doubl
     out[blockIdx.x * blockDim.x + threadIdx.x] = s;
 }
 
+// The same with the accumulator in the addend slot and one per-thread register as both factors,
+// x[c] = fma(u[k], u[k], x[c]): two distinct register sources per DFMA.  On B200 this shape retires 63.7 of the
+// nominal 64 lanes per clock per SM (the x = fma(x, a, b) shape above stops at 57.8, three distinct register
+// sources at 48: tools/fp64_mix.cu, profiles/r01_fp64_mix_v5.md), so it is the one that sets the peak.
+template <int NCH>
+__global__ void __launch_bounds__(256) k_dfma_peak_acc(double *out, int iters, double a, double b)
+{
+    double x[NCH], u[8];
+#pragma unroll
+    for (int c = 0; c < NCH; ++c) x[c] = (double)(threadIdx.x + c);
+#pragma unroll
+    for (int c = 0; c < 8; ++c) u[c] = a * 1e-3 + b * (double)(threadIdx.x * 8 + c);
+    for (int it = 0; it < iters; ++it)
+    {
+#pragma unroll
+        for (int q = 0; q < 64 / NCH; ++q)
+#pragma unroll
+            for (int c = 0; c < NCH; ++c) x[c] = fma(u[(c + q) % 8], u[(c + q) % 8], x[c]);
+    }
+    double s = 0.0;
+#pragma unroll
+    for (int c = 0; c < NCH; ++c) s += x[c];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
 }  // namespace gdy
