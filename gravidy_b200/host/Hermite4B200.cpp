@@ -1,7 +1,10 @@
 #include "Hermite4B200.hpp"
 
 #include <chrono>
+#include <cstdio>
 #include <cstdlib>
+#include <cstring>
+#include <fstream>
 #include <sstream>
 #include <thread>
 
@@ -165,6 +168,106 @@ gdy_run_stats Hermite4B200::run_until(double t_stop, double &ATIME, double &ITIM
     ITIME = st[0].itime;
     ns->gtime.update_end += st[0].force_ms * 1e-3;
     return st[0];
+}
+
+// ---- checkpoint ------------------------------------------------------------------------------------------
+// The reference can only resume from a TEXT snapshot (src/include/utils/Logger.cpp:77-111 writes it with 4-6
+// digits, src/include/utils/OptionsParser.cpp:122-324 reads it back), i.e. it restarts from rounded
+// positions with freshly initialised forces and timesteps: the continued run is a different run.  The
+// checkpoint keeps what the loop needs in full precision — r, v, acc, jerk, t, dt, the loop counters and
+// the energy references — so that `--restart` continues the block-timestep schedule bit for bit
+// (a2, a3 and the old forces are rewritten by every step before they are read, so they are not part of it).
+namespace {
+struct CkptHeader
+{
+    char magic[8];
+    uint32_t n, snap_number, output_factor, iterations, nsteps, reserved;
+    int64_t interactions;
+    double e2;
+    float eta, reserved2;
+    double ITIME, ATIME, e_ini, e_tmp;
+};
+const char CKPT_MAGIC[8] = {'G', 'D', 'Y', 'C', 'K', 'P', 'T', '1'};
+}  // namespace
+
+void Hermite4B200::write_checkpoint(const LoopState &ls)
+{
+    refresh_mirrors(true);
+    CkptHeader h;
+    std::memset(&h, 0, sizeof(h));
+    std::memcpy(h.magic, CKPT_MAGIC, 8);
+    h.n = ns->n; h.snap_number = ls.snap_number; h.output_factor = ls.output_factor;
+    h.iterations = ns->iterations; h.nsteps = ls.nsteps; h.interactions = ls.interactions;
+    h.e2 = ns->e2; h.eta = ns->eta;
+    h.ITIME = ls.ITIME; h.ATIME = ls.ATIME; h.e_ini = ns->en.ini; h.e_tmp = ns->en.tmp;
+    const std::string name = ns->output_filename + ".ckpt", tmp = name + ".tmp";
+    {
+        std::ofstream out(tmp.c_str(), std::ios::out | std::ios::binary | std::ios::trunc);
+        const size_t n = ns->n;
+        out.write(reinterpret_cast<const char *>(&h), sizeof(h));
+        out.write(reinterpret_cast<const char *>(ns->h_r), n * sizeof(double4));
+        out.write(reinterpret_cast<const char *>(ns->h_v), n * sizeof(double4));
+        out.write(reinterpret_cast<const char *>(ns->h_f), n * sizeof(Forces));
+        out.write(reinterpret_cast<const char *>(ns->h_t), n * sizeof(double));
+        out.write(reinterpret_cast<const char *>(ns->h_dt), n * sizeof(double));
+        if (!out.good())
+        {
+            logger->log_error("cannot write " + tmp);
+            std::exit(EXIT_FAILURE);
+        }
+    }
+    // the previous checkpoint stays valid until the new one is complete
+    if (std::rename(tmp.c_str(), name.c_str()))
+    {
+        logger->log_error("cannot rename " + tmp + " to " + name);
+        std::exit(EXIT_FAILURE);
+    }
+}
+
+void Hermite4B200::read_checkpoint(LoopState &ls)
+{
+    std::ifstream in(ns->restart_filename.c_str(), std::ios::in | std::ios::binary);
+    CkptHeader h;
+    in.read(reinterpret_cast<char *>(&h), sizeof(h));
+    if (!in.good() || std::memcmp(h.magic, CKPT_MAGIC, 8) != 0)
+    {
+        logger->log_error(ns->restart_filename + " is not a gravidy-b200 checkpoint");
+        std::exit(EXIT_FAILURE);
+    }
+    if (h.n != ns->n)
+    {
+        std::ostringstream m;
+        m << ns->restart_filename << " holds " << h.n << " particles, the input file " << ns->n;
+        logger->log_error(m.str());
+        std::exit(EXIT_FAILURE);
+    }
+    if (h.e2 != ns->e2 || h.eta != ns->eta)
+        logger->log_warning("softening/eta differ from the checkpointed run: the schedule will not be the same");
+    if (!(h.ITIME < (double)ns->integration_time))
+    {
+        logger->log_error("the checkpoint is already at or past the requested integration time (-t)");
+        std::exit(EXIT_FAILURE);
+    }
+    const size_t n = ns->n;
+    in.read(reinterpret_cast<char *>(ns->h_r), n * sizeof(double4));
+    in.read(reinterpret_cast<char *>(ns->h_v), n * sizeof(double4));
+    in.read(reinterpret_cast<char *>(ns->h_f), n * sizeof(Forces));
+    in.read(reinterpret_cast<char *>(ns->h_t), n * sizeof(double));
+    in.read(reinterpret_cast<char *>(ns->h_dt), n * sizeof(double));
+    if (!in.good())
+    {
+        logger->log_error(ns->restart_filename + " is truncated");
+        std::exit(EXIT_FAILURE);
+    }
+    ls.ITIME = h.ITIME; ls.ATIME = h.ATIME; ls.nsteps = h.nsteps; ls.output_factor = h.output_factor;
+    ls.snap_number = h.snap_number; ls.interactions = h.interactions;
+    ns->iterations = h.iterations;
+    ns->en.ini = h.e_ini; ns->en.tmp = h.e_tmp;
+    each_shard([&](int g) {
+        check(gdy_upload_particles(shards[g], &ns->h_r[0].x, &ns->h_v[0].x), g, "gdy_upload_particles");
+        check(gdy_upload_forces(shards[g], &ns->h_f[0].a[0]), g, "gdy_upload_forces");
+        check(gdy_upload_times(shards[g], ns->h_t, ns->h_dt), g, "gdy_upload_times");
+    });
 }
 
 }  // namespace gravidy

@@ -42,6 +42,16 @@ private:
     void upload_times();                 // h_t, h_dt -> device (after the host init_dt)
     void refresh_mirrors(bool forces);   // device -> h_r, h_v (, h_f, h_t, h_dt) at output points
     gdy_run_stats run_until(double t_stop, double &ATIME, double &ITIME);
+
+    // binary full-precision checkpoint: everything the loop needs to go on bit for bit
+    struct LoopState
+    {
+        double ITIME, ATIME;
+        unsigned int nsteps, output_factor, snap_number;
+        long long interactions;
+    };
+    void write_checkpoint(const LoopState &ls);
+    void read_checkpoint(LoopState &ls);
 };
 
 }  // namespace gravidy

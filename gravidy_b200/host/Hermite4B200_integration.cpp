@@ -28,32 +28,52 @@ void Hermite4B200::integration()
     long long interactions = 0;            // 64-bit (the reference's nact * n wraps at 2^32)
     unsigned int output_factor = 1;
 
-    init_acc_jrk();
-    init_dt(ATIME, ETA_S, ITIME);
-    upload_times();
-
-    ns->en.ini = get_energy_gpu();
-    ns->en.tmp = ns->en.ini;
-
-    nu->nbody_attributes();
-
-    logger->print_info();
-    logger->write_info();
-    logger->print_energy_log(ITIME, ns->iterations, interactions, nsteps, ns->en.ini);
-
     unsigned int snap_number = ns->snapshot_number;
-    logger->write_snapshot(snap_number, ITIME);
-    snap_number++;
-
-    if (ns->ops.print_all) logger->print_all(ITIME, snap_number);
-    if (ns->ops.print_lagrange)
+    const bool restart = !ns->restart_filename.empty();
+    if (restart)
     {
-        nu->lagrange_radii();
-        logger->print_lagrange_radii(ITIME, nu->layers_radii);
+        // --restart: r, v, acc, jerk, t, dt and the loop counters come from the checkpoint in full precision;
+        // no init_acc_jrk / init_dt, no second snapshot of the restart time
+        LoopState ls;
+        read_checkpoint(ls);
+        ITIME = ls.ITIME; ATIME = ls.ATIME; nsteps = ls.nsteps; interactions = ls.interactions;
+        output_factor = ls.output_factor; snap_number = ls.snap_number;
+        nu->nbody_attributes();
+        logger->print_info();
+        logger->write_info();
+        const double e_tmp = ns->en.tmp;
+        logger->print_energy_log(ITIME, ns->iterations, interactions, nsteps, get_energy_gpu());
+        ns->en.tmp = e_tmp;   // RelE of the next line stays relative to the last line of the checkpointed run
+    }
+    else
+    {
+        init_acc_jrk();
+        init_dt(ATIME, ETA_S, ITIME);
+        upload_times();
+
+        ns->en.ini = get_energy_gpu();
+        ns->en.tmp = ns->en.ini;
+
+        nu->nbody_attributes();
+
+        logger->print_info();
+        logger->write_info();
+        logger->print_energy_log(ITIME, ns->iterations, interactions, nsteps, ns->en.ini);
+
+        logger->write_snapshot(snap_number, ITIME);
+        snap_number++;
+
+        if (ns->ops.print_all) logger->print_all(ITIME, snap_number);
+        if (ns->ops.print_lagrange)
+        {
+            nu->lagrange_radii();
+            logger->print_lagrange_radii(ITIME, nu->layers_radii);
+        }
     }
 
     while (ITIME < ns->integration_time)
     {
+        bool wrote_output = false;
         if (ns->hooks_mode)
         {
             ITIME = ATIME;
@@ -92,13 +112,17 @@ void Hermite4B200::integration()
             logger->write_snapshot(snap_number, ITIME);
             snap_number++;
             output_factor += 1;
+            wrote_output = true;
         }
 
         nsteps += nact;
         ns->iterations++;
+        if (ns->checkpoint && wrote_output)
+            write_checkpoint(LoopState{ITIME, ATIME, nsteps, output_factor, snap_number, interactions});
     }
 
     ns->gtime.integration_end = now_s() - ns->gtime.integration_ini;
+    if (ns->checkpoint) write_checkpoint(LoopState{ITIME, ATIME, nsteps, output_factor, snap_number, interactions});
     refresh_mirrors(false);
     logger->write_snapshot(snap_number, ITIME);
     std::ostringstream s;

@@ -15,7 +15,7 @@ NbodySystem::NbodySystem(const OptionsParser &op)
       integration_time(op.integration_time), interval_time(op.interval_time),
       snapshot_time(op.snapshot_time), snapshot_number(op.snapshot_number),
       length_snap(op.length_output_number), resume(op.resume), ops(op.ops), gpus(op.gpus),
-      hooks_mode(op.hooks_mode)
+      hooks_mode(op.hooks_mode), checkpoint(op.checkpoint), restart_filename(op.restart_filename)
 {
     const float e2f = op.softening * op.softening;   // float arithmetic first, then widened
     e2 = e2f;

@@ -28,6 +28,8 @@ public:
     PrintOptions ops;
     int gpus;
     bool hooks_mode;
+    bool checkpoint;
+    std::string restart_filename;
     double e2;          // softening squared: FLOAT product widened (reference: NbodySystem.cpp:50)
     float eta;          // accuracy parameter, float as in the reference (NbodySystem.hpp:67)
 

@@ -18,7 +18,7 @@ const OptSpec SPECS[] = {
     {"help", 'h', false},     {"input", 'i', true},    {"time", 't', true},   {"resume", 'r', true},
     {"output", 'o', true},    {"softening", 's', true}, {"eta", 'e', true},    {"screen", 'p', false},
     {"interval", 'z', true},  {"lagrange", 'l', false}, {"all", 'a', false},   {"gpu", 'g', true},
-    {"hooks", 0, false},
+    {"hooks", 0, false},      {"checkpoint", 0, false}, {"restart", 0, true},
 };
 const OptSpec *find_long(const std::string &n)
 {
@@ -95,7 +95,11 @@ std::string OptionsParser::usage() const
       << "  -g [ --gpu ] <value> (=0)       GPUs to use, by default is the maximum available\n"
       << "                                  devices (1, 2, 4 or 8 j-shards)\n"
       << "  --hooks                         Drive every block step through the individual hooks\n"
-      << "                                  instead of the fused device driver (same results)\n";
+      << "                                  instead of the fused device driver (same results)\n"
+      << "  --checkpoint                    Write <output>.ckpt (binary, full precision: r, v, acc, jerk,\n"
+      << "                                  t, dt, counters) at every output time and at the end\n"
+      << "  --restart <filename>.ckpt       Continue the run of -i <filename> from a checkpoint: the\n"
+      << "                                  block-timestep schedule goes on exactly where it stopped\n";
     return u.str();
 }
 
@@ -118,6 +122,21 @@ bool OptionsParser::check_options()
         return false;
     }
     hooks_mode = has("hooks");
+    checkpoint = has("checkpoint");
+    if (has("restart"))
+    {
+        restart_filename = given["restart"];
+        if (!file_exists(restart_filename))
+        {
+            std::cerr << "gravidy: cannot access " << restart_filename << ": No such file or directory" << std::endl;
+            return false;
+        }
+        if (has("resume"))
+        {
+            std::cerr << "gravidy: --restart and --resume exclude each other" << std::endl << usage() << std::endl;
+            return false;
+        }
+    }
     auto as_float = [&](const char *name) { return (float)strtod(given[name].c_str(), nullptr); };
     const bool time_given = true;   // "-t" has a default value of 1 in the reference, so it always counts
     integration_time = has("time") ? as_float("time") : 1.0f;

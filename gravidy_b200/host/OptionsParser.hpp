@@ -28,6 +28,8 @@ public:
     bool resume = false;
     PrintOptions ops;
     bool hooks_mode = false;   // --hooks: drive the loop hook by hook instead of the fused device driver
+    bool checkpoint = false;   // --checkpoint: binary full-precision state beside the text snapshots
+    std::string restart_filename;   // --restart: continue from such a checkpoint
 
     bool file_exists(const std::string &filename) const;
     bool check_options();

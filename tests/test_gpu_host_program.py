@@ -106,6 +106,62 @@ def test_lagrange_radii_and_resume(binary, tmp_path):
     assert log[1].split()[1] == "0.250" and log[-1].split()[1] == "0.375"
 
 
+CKPT_HEADER = np.dtype([("magic", "S8"), ("n", "<u4"), ("snap_number", "<u4"), ("output_factor", "<u4"),
+                        ("iterations", "<u4"), ("nsteps", "<u4"), ("reserved", "<u4"), ("interactions", "<i8"),
+                        ("e2", "<f8"), ("eta", "<f4"), ("reserved2", "<f4"), ("ITIME", "<f8"), ("ATIME", "<f8"),
+                        ("e_ini", "<f8"), ("e_tmp", "<f8")])
+
+
+def read_ckpt(path):
+    raw = open(path, "rb").read()
+    h = np.frombuffer(raw[:CKPT_HEADER.itemsize], dtype=CKPT_HEADER)[0]
+    n = int(h["n"])
+    body = np.frombuffer(raw[CKPT_HEADER.itemsize:], dtype="<f8")
+    assert body.size == n * (4 + 4 + 6 + 1 + 1)
+    o = np.cumsum([0, 4 * n, 4 * n, 6 * n, n, n])
+    r4, v4, f6, t, dt = (body[o[k]:o[k + 1]] for k in range(5))
+    return h, r4.reshape(n, 4), v4.reshape(n, 4), f6.reshape(n, 6), t, dt
+
+
+@pytest.mark.parametrize("mode", [[], ["--hooks"]])
+def test_checkpoint_restart_continues_the_schedule_bit_for_bit(binary, tmp_path, mode):
+    """run to t=0.5 straight, and to t=0.25 + --restart to t=0.5: the full-precision state
+    (r, v, acc, jerk, t, dt), every counter, the next block time and the text outputs are identical."""
+    a, b = tmp_path / "a", tmp_path / "b"
+    a.mkdir(); b.mkdir()
+    for d in (a, b):
+        shutil.copy(os.path.join(REF, "input.dat"), d / "input.dat")
+    common = [binary, "-i", "./input.dat", "-o", "./run", "--checkpoint"] + mode
+    p = subprocess.run(common + ["-t", "0.5"], cwd=a, capture_output=True, text=True, timeout=300)
+    assert p.returncode == 0, p.stderr
+    p = subprocess.run(common + ["-t", "0.25"], cwd=b, capture_output=True, text=True, timeout=300)
+    assert p.returncode == 0, p.stderr
+    half = read_ckpt(b / "run.out.ckpt")
+    assert half[0]["magic"] == b"GDYCKPT1" and half[0]["ITIME"] == 0.25 and half[0]["n"] == 64
+    shutil.copy(b / "run.out.ckpt", b / "half.ckpt")
+    p = subprocess.run(common + ["-t", "0.5", "--restart", "./half.ckpt"], cwd=b, capture_output=True, text=True,
+                       timeout=300)
+    assert p.returncode == 0, p.stderr
+    ha, hb = read_ckpt(a / "run.out.ckpt"), read_ckpt(b / "run.out.ckpt")
+    for name in CKPT_HEADER.names:
+        assert ha[0][name] == hb[0][name], name
+    assert ha[0]["ITIME"] == 0.5 and ha[0]["iterations"] > half[0]["iterations"]
+    for x, y in zip(ha[1:], hb[1:]):
+        assert np.array_equal(x, y)
+    # the snapshots of the second half and the final one are the same files
+    for f in ("run.out.snapshot_03", "run.out.snapshot_04", "run.out.snapshot_05"):
+        assert open(a / f).read() == open(b / f).read(), f
+    # energy log: the lines of t = 0.375 and 0.5 agree in everything but the wall-clock columns
+    la = [ln[:92] for ln in open(a / "run.out.log").read().splitlines()]
+    lb = [ln[:92] for ln in open(b / "run.out.log").read().splitlines()]
+    assert la[-2:] == lb[-2:]
+    # a checkpoint of another system, or one that is already past -t, is refused
+    p = subprocess.run(common + ["-t", "0.25", "--restart", "./half.ckpt"], cwd=b, capture_output=True, text=True)
+    assert p.returncode != 0 and "already at or past" in p.stderr
+    p = subprocess.run(common + ["-t", "0.5", "--restart", "./input.dat"], cwd=b, capture_output=True, text=True)
+    assert p.returncode != 0 and "not a gravidy-b200 checkpoint" in p.stderr
+
+
 def test_cli_errors(binary, tmp_path):
     p = subprocess.run([binary], capture_output=True, text=True)
     assert p.returncode == 1 and "option requires an argument -- 'input'" in p.stderr
