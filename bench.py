@@ -47,6 +47,8 @@ def parse_args():
     ap.add_argument("--no-integration", action="store_true")
     ap.add_argument("--integration-steps", type=int, default=400)
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
+    ap.add_argument("--cpu-loop-steps", type=int, default=100,
+                    help="block steps of the N-body loop the reference CPU code is timed on (cpu_baseline.loop)")
     return ap.parse_args()
 
 
@@ -255,14 +257,20 @@ def run_b200(args, m, r, v):
     integ = None
     if not args.no_integration:
         at = h.init_dt(0.0)
-        st, _, _ = h.run(at, 1e9, max_steps=50)
+        want_cpu_loop = rank == 0 and world == 1 and not args.no_cpu_baseline and args.cpu_loop_steps > 0
+        start = h.get_state("f6", "t", "dt") if want_cpu_loop else None   # the loop's initial state, for the CPU arm
+        k0 = max(args.cpu_loop_steps, 50)
+        barrier()
+        st, tn0, _, tu0 = h.run(at, 1e9, max_steps=k0, trace_cap=k0, trace_us=True)
+        barrier()
+        loop_head = {"atime0": at, "nact": tn0, "us": tu0}
         l1 = h.launch_count()
         barrier()
         st, tn, _, tu = h.run(st.atime, 1e9, max_steps=args.integration_steps,
                               trace_cap=args.integration_steps, itime0=st.itime, trace_us=True)
         barrier()
         wall = max_over_ranks(st.wall_ms) * 1e-3
-        integ = {"workload": f"block-timestep integration, Plummer N={n}, block steps 50..{50 + st.iterations}",
+        integ = {"workload": f"block-timestep integration, Plummer N={n}, block steps {k0}..{k0 + st.iterations}",
                  "block_steps": int(st.iterations), "sum_nact": int(st.nsteps),
                  "mean_nact": float(st.nsteps) / max(int(st.iterations), 1),
                  "median_nact": float(np.median(tn)) if len(tn) else None,
@@ -279,6 +287,32 @@ def run_b200(args, m, r, v):
                "kind": info["kind"],
                "sample": f"update_acc_jrk-style sweep of {info['nact']} of {n} i-particles x {n} j "
                          f"({info['seconds']:.1f} s), scaled to the full N^2"}
+        if integ is not None and args.cpu_loop_steps > 0:
+            # the same first block steps of the N-body loop on the host cores: the reference's own loop body
+            # (find_particles_to_move .. next_integration_time) from the state the GPU run started from
+            from oracle import oracle as O
+            o = O.best_oracle(m, r, v)
+            o.set_threads(info["cores"])
+            o.set_state(f6=start["f6"], t=start["t"], dt=start["dt"])
+            # bounded: as many of the first block steps as the CPU does in about 2 x --cpu-seconds
+            cum = np.cumsum(loop_head["nact"].astype(np.float64) * n)
+            k0 = int(min(args.cpu_loop_steps, max(1, np.searchsorted(cum, crate * 2.0 * args.cpu_seconds))))
+            loop_head["block_steps"] = k0
+            loop_head["pairs"] = int(cum[k0 - 1])
+            loop_head["gpu_wall_s"] = float(loop_head["us"][:k0].sum()) * 1e-6
+            t0 = time.perf_counter()
+            so, tno, _ = o.run(loop_head["atime0"], 1e9, max_steps=k0, trace_cap=k0)
+            cpu_wall = time.perf_counter() - t0
+            cpu["loop"] = {"workload": f"block-timestep loop, Plummer N={n}, block steps 0..{k0}",
+                           "block_steps": int(so.iterations), "pairs": int(so.interactions),
+                           "cpu_wall_s": cpu_wall, "gpu_wall_s": loop_head["gpu_wall_s"],
+                           "cpu_gflops": so.interactions * FLOP_PER_PAIR / cpu_wall / 1e9,
+                           "gpu_gflops": loop_head["pairs"] * FLOP_PER_PAIR / loop_head["gpu_wall_s"] / 1e9,
+                           "gpu_over_cpu_wall": cpu_wall / loop_head["gpu_wall_s"],
+                           "schedule_identical": bool(np.array_equal(tno, loop_head["nact"][:k0])
+                                                      and int(so.interactions) == loop_head["pairs"]),
+                           "kind": o.kind, "cores": info["cores"]}
+            o.close()
 
     if rank == 0:
         line = {
