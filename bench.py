@@ -229,6 +229,26 @@ def run_b200(args, m, r, v):
     # the dominant kernel alone (rank-local j-shard, no allreduce): same number at 1 GPU
     kern_tf = (pairs / world) * FLOP_PER_PAIR / (float(np.mean(ms)) * 1e-3) / 1e12
 
+    # ---- the memory-bound kernel of the step: the predictor (120 B read + 48 B written per particle) ----
+    pred_ms = []
+    for _ in range(3 + 5):
+        flush.zero_()
+        torch.cuda.synchronize()
+        pred_ms.append(h.predict_timed(0.0))
+    pred_ms = float(np.mean(pred_ms[3:]))
+    hbm_peak, hbm_src = 6551.4, "fallback: the B200 copy bandwidth of MEASURED_PEAKS.json on this pool (file absent)"
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            hbm_peak, hbm_src = float(json.load(f)["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (copy, read+write bytes)"
+    except Exception:
+        pass
+    pred_gbs = 168.0 * n / (pred_ms * 1e-3) / 1e9
+    roofline_hbm = {"bound": "hbm", "kernel": "k_predict (predicted_pos_vel, all N, L2 flushed before each launch)",
+                    "achieved": pred_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": pred_gbs / hbm_peak,
+                    "us_per_launch": pred_ms * 1e3, "algorithmic_bytes_per_particle": 168, "traffic": None,
+                    "peak_source": hbm_src,
+                    "note": "at this N the launch is ~8 us: latency- as much as bandwidth-bound"}
+
     # ---- e2e: host buffers through the C ABI, copies inside the timed region --------------------------
     r4 = torch.empty((n, 4), dtype=torch.float64).pin_memory().numpy()
     v4 = torch.empty((n, 4), dtype=torch.float64).pin_memory().numpy()
@@ -338,6 +358,7 @@ def run_b200(args, m, r, v):
                          "peak_equiv_sm_mhz_at_64_dfma_per_clk_per_sm": peak_mhz,
                          "nominal_peak_at_max_clock": 2.0 * 64 * 148 * 1965e6 / 1e12,
                          "flop_convention": "60 flop/pair; the kernel issues 31 FP64 instructions/pair"},
+            "roofline_hbm": roofline_hbm,
             "e2e": e2e, "gpu_launches": int(launches), "clocks": sampler.summary(),
             "integration": integ, "cpu_baseline": cpu, "wall_timed_s": wall_timed,
         }

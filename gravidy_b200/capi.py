@@ -66,6 +66,7 @@ SIGNATURES = {
                           C.POINTER(RunStats), _up, _dp, _fp, C.c_uint64]),
     "gdy_force_sweep": (C.c_int, [_ctx, C.c_uint32, _up, _dp, _fp]),
     "gdy_force_sweep_full": (C.c_int, [_ctx, C.c_int, _fp]),
+    "gdy_predict_timed": (C.c_int, [_ctx, C.c_double, _fp]),
     "gdy_set_tuning": (C.c_int, [_ctx, C.c_int, C.c_int]),
     "gdy_set_persist": (C.c_int, [_ctx, C.c_int]),
     "gdy_persist_stats": (C.c_int, [_ctx, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),

@@ -772,6 +772,24 @@ extern "C" int gdy_predicted_pos_vel(gdy_ctx *c, double itime)
     return GDY_OK;
 }
 
+// The same launch bracketed by events: the predictor is the memory-bound kernel of the step (120 B read +
+// 48 B written per particle), bench.py reports its GB/s against the measured HBM copy bandwidth.
+extern "C" int gdy_predict_timed(gdy_ctx *c, double itime, float *ms_out)
+{
+    if (!c || !ms_out) return GDY_ERR_INVALID;
+    BIND(c);
+    int r;
+    if ((r = need_particles(c))) return r;
+    CU(cudaEventRecord(c->ev0, c->st));
+    k_predict<<<cdiv(c->n, 256), 256, 0, c->st>>>(c->s, 0, c->n, itime, nullptr, 0);
+    LAUNCHED(c);
+    CU(cudaEventRecord(c->ev1, c->st));
+    CU(cudaStreamSynchronize(c->st));
+    CU(cudaEventElapsedTime(ms_out, c->ev0, c->ev1));
+    c->have_pred = true;
+    return GDY_OK;
+}
+
 extern "C" int gdy_update_acc_jrk(gdy_ctx *c, uint32_t nact)
 {
     if (!c) return GDY_ERR_INVALID;

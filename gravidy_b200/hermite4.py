@@ -209,6 +209,12 @@ class Hermite4B200:
         self._ck(self.lib.gdy_force_sweep_full(self.h, reps, C.byref(ms)))
         return ms.value
 
+    def predict_timed(self, itime):
+        """predicted_pos_vel(itime) for all N, returns the kernel's milliseconds (CUDA events)."""
+        ms = C.c_float()
+        self._ck(self.lib.gdy_predict_timed(self.h, itime, C.byref(ms)))
+        return ms.value
+
     def set_tuning(self, variant=-1, jsplit=-1):
         self._ck(self.lib.gdy_set_tuning(self.h, variant, jsplit))
 

@@ -164,6 +164,10 @@ int gdy_force_sweep(gdy_ctx *ctx, uint32_t nact, const uint32_t *move, double *f
 /* Same, nact = n, identity list, no host traffic: `reps` back-to-back evaluations, mean ms. */
 int gdy_force_sweep_full(gdy_ctx *ctx, int reps, float *ms_out);
 
+/* gdy_predicted_pos_vel bracketed by CUDA events (bench: GB/s of the memory-bound predictor kernel;
+ * replaces k_prediction, reference: src/include/gpu/Hermite4GPU_kernels.cu:127-158). */
+int gdy_predict_timed(gdy_ctx *ctx, double itime, float *ms_out);
+
 /* Force-kernel variant override for tuning (-1 = heuristic). */
 int gdy_set_tuning(gdy_ctx *ctx, int variant, int jsplit);
 
