@@ -162,6 +162,51 @@ def test_checkpoint_restart_continues_the_schedule_bit_for_bit(binary, tmp_path,
     assert p.returncode != 0 and "not a gravidy-b200 checkpoint" in p.stderr
 
 
+def _gpu_count():
+    try:
+        import torch
+        return torch.cuda.device_count()
+    except Exception:
+        return 0
+
+
+@pytest.mark.skipif(_gpu_count() < 2, reason="needs 2 GPUs (gpurun --gpus 2)")
+def test_two_gpu_host_program_writes_the_same_files(binary, tmp_path):
+    """-g 2: one thread per GPU inside the host program, j-sharded, NCCL for big blocks and the fused NVLink
+    exchange (same-process peer access) for small ones.  Same schedule and the same text outputs as -g 1
+    (forces differ by summation order only, far below the printed digits), and a checkpoint written on two
+    GPUs restarts on one."""
+    a, b = tmp_path / "a", tmp_path / "b"
+    a.mkdir(); b.mkdir()
+    run_host(binary, a, ["-g", "1", "--checkpoint"])
+    run_host(binary, b, ["-g", "2", "--checkpoint"])
+    for f in sorted(os.listdir(a)):
+        if not f.startswith("run.out") or f.endswith(".ckpt"):
+            continue
+        x, y = open(a / f).read(), open(b / f).read()
+        if f.endswith(".log"):
+            gx, gy = numbers(x), numbers(y)
+            assert np.array_equal(gx[:, :4], gy[:, :4])                 # tag, time, Iter, Nsteps: exact
+            np.testing.assert_allclose(gx[:, 4], gy[:, 4], rtol=1e-12)  # energy
+        elif f.endswith(".info"):
+            assert x == y
+        else:
+            same_layout(x, y)
+            np.testing.assert_allclose(numbers(x), numbers(y), rtol=1e-9, atol=1e-14)
+    ha, hb = read_ckpt(a / "run.out.ckpt"), read_ckpt(b / "run.out.ckpt")
+    for name in ("n", "snap_number", "output_factor", "iterations", "nsteps", "interactions", "ITIME", "ATIME"):
+        assert ha[0][name] == hb[0][name], name
+    assert np.array_equal(ha[4], hb[4]) and np.array_equal(ha[5], hb[5])   # t, dt: the schedule
+    np.testing.assert_allclose(ha[1], hb[1], rtol=1e-10, atol=1e-14)
+    # restart the 2-GPU checkpoint on one GPU
+    shutil.copy(b / "run.out.ckpt", b / "two.ckpt")
+    p = subprocess.run([binary, "-i", "./input.dat", "-o", "./run", "-t", "0.625", "-g", "1", "--restart", "./two.ckpt"],
+                       cwd=b, capture_output=True, text=True, timeout=300)
+    assert p.returncode == 0, p.stderr
+    log = open(b / "run.out.log").read().splitlines()
+    assert log[-1].split()[1] == "0.625"
+
+
 def test_cli_errors(binary, tmp_path):
     p = subprocess.run([binary], capture_output=True, text=True)
     assert p.returncode == 1 and "option requires an argument -- 'input'" in p.stderr
