@@ -9,7 +9,8 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libgravidy_b200.so")
+# GDY_LIB: a lab build of the same library (tools/force_lab.sh compiles inner-loop variants side by side)
+LIB_PATH = os.environ.get("GDY_LIB") or os.path.join(HERE, "libgravidy_b200.so")
 
 _dp = C.POINTER(C.c_double)
 _up = C.POINTER(C.c_uint32)

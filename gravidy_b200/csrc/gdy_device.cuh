@@ -156,4 +156,75 @@ __device__ __forceinline__ void pair(Acc6 &s, double xi, double yi, double zi, d
     s.jz = fma(mr3, fma(c, dz, dvz), s.jz);
 }
 
+
+// The same pair in two halves: pair_head leaves (d, dv, m/r^3, c) in registers, pair_tail does the nine
+// three-source DFMAs.  Written apart so that the DFMAs that share m/r^3 (six) and c (three) can sit next to each
+// other in the SASS: an operand the previous DFMA of the warp flagged `.reuse` is not read from the register file,
+// which is what limits a three-source DFMA to 3/4 rate (tools/fp64_reuse.cu, profiles/r01_fp64_reuse_v9.md).
+struct PairMid { double dx, dy, dz, dvx, dvy, dvz, mr3, c; };
+
+template <bool MASK_SELF>
+__device__ __forceinline__ PairMid pair_head(double xi, double yi, double zi, double vxi, double vyi, double vzi,
+                                             double xj, double yj, double zj, double vxj, double vyj, double vzj,
+                                             double mj, double e2)
+{
+    PairMid p;
+    p.dx = xj - xi; p.dy = yj - yi; p.dz = zj - zi;
+    p.dvx = vxj - vxi; p.dvy = vyj - vyi; p.dvz = vzj - vzi;
+    double r2 = fma(p.dx, p.dx, e2);
+    r2 = fma(p.dy, p.dy, r2);
+    r2 = fma(p.dz, p.dz, r2);
+    double rv = p.dx * p.dvx;
+    rv = fma(p.dy, p.dvy, rv);
+    rv = fma(p.dz, p.dvz, rv);
+    double y = rsqrt_f64(r2);
+    if (MASK_SELF) y = (r2 > 0.0) ? y : 0.0;
+    const double y2 = y * y;
+    p.mr3 = (mj * y) * y2;
+    p.c = (rv * y2) * (-3.0);
+    return p;
+}
+
+__device__ __forceinline__ void pair_tail(Acc6 &s, const PairMid &p)
+{
+    const double tx = fma(p.c, p.dx, p.dvx);
+    const double ty = fma(p.c, p.dy, p.dvy);
+    const double tz = fma(p.c, p.dz, p.dvz);
+    s.ax = fma(p.mr3, p.dx, s.ax);
+    s.ay = fma(p.mr3, p.dy, s.ay);
+    s.az = fma(p.mr3, p.dz, s.az);
+    s.jx = fma(p.mr3, tx, s.jx);
+    s.jy = fma(p.mr3, ty, s.jy);
+    s.jz = fma(p.mr3, tz, s.jz);
+}
+
+// Software-pipelined halves (GDY_FORCE_FORM 3): pair_head7 also does t = c*d + dv, so that what is carried to the
+// next trip is (d, t, m/r^3) and the tail is six DFMAs that all share m/r^3.  A zeroed PairCarry adds exactly 0.
+struct PairCarry { double dx, dy, dz, tx, ty, tz, mr3; };
+
+template <bool MASK_SELF>
+__device__ __forceinline__ PairCarry pair_head7(double xi, double yi, double zi, double vxi, double vyi, double vzi,
+                                                double xj, double yj, double zj, double vxj, double vyj, double vzj,
+                                                double mj, double e2)
+{
+    const PairMid p = pair_head<MASK_SELF>(xi, yi, zi, vxi, vyi, vzi, xj, yj, zj, vxj, vyj, vzj, mj, e2);
+    PairCarry c;
+    c.dx = p.dx; c.dy = p.dy; c.dz = p.dz;
+    c.tx = fma(p.c, p.dx, p.dvx);
+    c.ty = fma(p.c, p.dy, p.dvy);
+    c.tz = fma(p.c, p.dz, p.dvz);
+    c.mr3 = p.mr3;
+    return c;
+}
+
+__device__ __forceinline__ void pair_tail6(Acc6 &s, const PairCarry &p)
+{
+    s.ax = fma(p.mr3, p.dx, s.ax);
+    s.ay = fma(p.mr3, p.dy, s.ay);
+    s.az = fma(p.mr3, p.dz, s.az);
+    s.jx = fma(p.mr3, p.tx, s.jx);
+    s.jy = fma(p.mr3, p.ty, s.jy);
+    s.jz = fma(p.mr3, p.tz, s.jz);
+}
+
 }  // namespace gdy

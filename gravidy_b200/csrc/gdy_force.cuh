@@ -23,6 +23,24 @@
 #pragma once
 #include "gdy_device.cuh"
 
+// Inner-loop form of k_force_warp.  0 = one pair() after the other; 1 = heads of the 2 x IPT pairs of a trip, then
+// their tails (pair_head / pair_tail; putting a tail into ONE asm statement changes nothing: ptxas reorders it);
+// 3 = software-pipelined: the six-DFMA tails of the previous trip's pairs, which all share m/r^3, issue while this
+// trip's LDS.128 are in flight, then this trip's heads.  tools/force_lab.sh builds them side by side;
+// measured (profiles/r01_force_lab_v9.md): form 3, unroll 1, 512 resident threads is the fastest, 508 Gpairs/s.
+#ifndef GDY_FORCE_FORM
+#define GDY_FORCE_FORM 3
+#endif
+#ifndef GDY_FORCE_UNROLL
+#define GDY_FORCE_UNROLL 1
+#endif
+// threads the warp kernels are compiled to keep resident per SM (register cap = 65536 / this)
+#ifndef GDY_FORCE_RESIDENT
+#define GDY_FORCE_RESIDENT 512
+#endif
+#define GDY_STR_(x) #x
+#define GDY_UNROLL(n) _Pragma(GDY_STR_(unroll n))
+
 namespace gdy {
 
 // Arguments common to every force kernel (one struct: one signature, one launch table).
@@ -51,7 +69,7 @@ __device__ __forceinline__ IReg load_i(const ForceArgs &a, uint32_t k)
 
 // ------------------------------------------------------------------------------------------------------
 template <int IPT, int WI, int WJ, int NST, bool MASK>
-__global__ void __launch_bounds__(32 * WI * WJ)
+__global__ void __launch_bounds__(32 * WI * WJ, GDY_FORCE_RESIDENT / (32 * WI * WJ))
 k_force_warp(const ForceArgs a)
 {
     constexpr int NW = WI * WJ;
@@ -102,13 +120,18 @@ k_force_warp(const ForceArgs a)
         acc[q] = Acc6{0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
     }
     const double e2 = a.e2;
+#if GDY_FORCE_FORM == 3
+    PairCarry pc[2 * IPT];
+#pragma unroll
+    for (int q = 0; q < 2 * IPT; ++q) pc[q] = PairCarry{0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+#endif
 
     for (int t = 0; t < nt; ++t)
     {
         const int s = t % NST;
         mbar_wait(&myfull[s], (uint32_t)(t / NST) & 1u);
         const double *b = myring + (size_t)s * JBD;
-#pragma unroll 2
+        GDY_UNROLL(GDY_FORCE_UNROLL)
         for (int jj = 0; jj < JB; jj += 2)
         {
             const double2 X = *reinterpret_cast<const double2 *>(b + 0 * JB + jj);
@@ -118,6 +141,33 @@ k_force_warp(const ForceArgs a)
             const double2 VY = *reinterpret_cast<const double2 *>(b + 4 * JB + jj);
             const double2 VZ = *reinterpret_cast<const double2 *>(b + 5 * JB + jj);
             const double2 M = *reinterpret_cast<const double2 *>(b + 6 * JB + jj);
+#if GDY_FORCE_FORM == 3
+            // software pipeline: the six-DFMA tails of the previous trip's pairs issue while this trip's LDS.128
+            // are in flight, then this trip's heads
+#pragma unroll
+            for (int q = 0; q < 2 * IPT; ++q) pair_tail6(acc[q % IPT], pc[q]);
+#pragma unroll
+            for (int q = 0; q < IPT; ++q)
+                pc[q] = pair_head7<MASK>(ri[q].x, ri[q].y, ri[q].z, ri[q].vx, ri[q].vy, ri[q].vz, X.x, Y.x, Z.x,
+                                         VX.x, VY.x, VZ.x, M.x, e2);
+#pragma unroll
+            for (int q = 0; q < IPT; ++q)
+                pc[IPT + q] = pair_head7<MASK>(ri[q].x, ri[q].y, ri[q].z, ri[q].vx, ri[q].vy, ri[q].vz, X.y, Y.y,
+                                               Z.y, VX.y, VY.y, VZ.y, M.y, e2);
+#elif GDY_FORCE_FORM == 1
+            // heads of the 2 x IPT pairs of this trip, then their nine-DFMA tails
+            PairMid pm[2 * IPT];
+#pragma unroll
+            for (int q = 0; q < IPT; ++q)
+                pm[q] = pair_head<MASK>(ri[q].x, ri[q].y, ri[q].z, ri[q].vx, ri[q].vy, ri[q].vz, X.x, Y.x, Z.x,
+                                        VX.x, VY.x, VZ.x, M.x, e2);
+#pragma unroll
+            for (int q = 0; q < IPT; ++q)
+                pm[IPT + q] = pair_head<MASK>(ri[q].x, ri[q].y, ri[q].z, ri[q].vx, ri[q].vy, ri[q].vz, X.y, Y.y,
+                                              Z.y, VX.y, VY.y, VZ.y, M.y, e2);
+#pragma unroll
+            for (int q = 0; q < 2 * IPT; ++q) pair_tail(acc[q % IPT], pm[q]);
+#else
 #pragma unroll
             for (int q = 0; q < IPT; ++q)
                 pair<MASK>(acc[q], ri[q].x, ri[q].y, ri[q].z, ri[q].vx, ri[q].vy, ri[q].vz, X.x, Y.x, Z.x,
@@ -126,6 +176,7 @@ k_force_warp(const ForceArgs a)
             for (int q = 0; q < IPT; ++q)
                 pair<MASK>(acc[q], ri[q].x, ri[q].y, ri[q].z, ri[q].vx, ri[q].vy, ri[q].vz, X.y, Y.y, Z.y,
                            VX.y, VY.y, VZ.y, M.y, e2);
+#endif
         }
         __syncwarp();   // every lane is done with stage s -> it may be refilled
         if (lane == 0 && t + NST < nt)
@@ -134,6 +185,11 @@ k_force_warp(const ForceArgs a)
             issue(t + NST);
         }
     }
+
+#if GDY_FORCE_FORM == 3
+#pragma unroll
+    for (int q = 0; q < 2 * IPT; ++q) pair_tail6(acc[q % IPT], pc[q]);
+#endif
 
     double *out = a.part + (size_t)blockIdx.y * 6 * a.ld;
     if (WJ == 1)
