@@ -33,7 +33,7 @@ sys.path.insert(0, ROOT)
 FLOP_PER_PAIR = 60.0
 METRIC = "hermite_fp64_gflops_60flop_per_pair_N256k"
 UNIT = "GFLOP/s"
-NCU_DRAM_BYTES_PER_LAUNCH = 14909440 + 2216448   # profiles/r01_force_warp_ncu_v3.md
+NCU_DRAM_BYTES_PER_LAUNCH = 16292608 + 2715392   # profiles/r01_force_warp_ncu_v9.md
 
 
 def parse_args():
@@ -247,7 +247,27 @@ def run_b200(args, m, r, v):
                     "achieved": pred_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": pred_gbs / hbm_peak,
                     "us_per_launch": pred_ms * 1e3, "algorithmic_bytes_per_particle": 168, "traffic": None,
                     "peak_source": hbm_src,
-                    "note": "at this N the launch is ~8 us: latency- as much as bandwidth-bound"}
+                    "note": "one event-bracketed launch of ~10 us: launch latency is a third of it"}
+    # the same kernel where it is bandwidth-bound: N = 2M (352 MB per launch, nothing survives in the 126 MB L2),
+    # launches back to back — what the kernel sustains once launch latency is amortised
+    if rank == 0 and world == 1:
+        nb = 2097152
+        rng = np.random.default_rng(7)
+        hb = Hermite4B200(np.full(nb, 1.0 / nb), rng.standard_normal((nb, 3)), rng.standard_normal((nb, 3)),
+                          softening=1e-4, eta=0.01, device=local)
+        for _ in range(3):
+            hb.predict_timed(0.0)
+        reps = 20
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        big_ms = float(np.mean([hb.predict_timed(0.125 * (k + 1)) for k in range(reps)]))
+        big_wall = (time.perf_counter() - t0) / reps * 1e3
+        hb.close()
+        big_gbs = 168.0 * nb / (big_ms * 1e-3) / 1e9
+        roofline_hbm["bandwidth_regime"] = {"n": nb, "us_per_launch": big_ms * 1e3, "achieved": big_gbs,
+                                            "frac": big_gbs / hbm_peak, "wall_us_per_call": big_wall * 1e3,
+                                            "note": "same k_predict at N = 2M, working set 352 MB > L2, "
+                                                    "event-bracketed launches back to back"}
 
     # ---- e2e: host buffers through the C ABI, copies inside the timed region --------------------------
     r4 = torch.empty((n, 4), dtype=torch.float64).pin_memory().numpy()
@@ -350,7 +370,7 @@ def run_b200(args, m, r, v):
                          "traffic": NCU_DRAM_BYTES_PER_LAUNCH if (n == 262144 and world == 1) else None,
                          "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of one ncu --set full "
                                            "capture of this kernel at N=262144 on 1 GPU "
-                                           "(profiles/r01_force_warp_ncu_v3.md): 14.91 MB + 2.22 MB; "
+                                           "(profiles/r01_force_warp_ncu_v9.md): 16.29 MB + 2.72 MB; "
                                            "algorithmic 14.7 MB in + 12.6 MB out",
                          "kernel": "k_force_warp<IPT=2,WI=4,WJ=1,NST=3>",
                          "peak_source": "DFMA micro-benchmark on this GPU (gdy_measure_fp64_peak); "
