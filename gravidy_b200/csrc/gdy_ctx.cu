@@ -115,7 +115,8 @@ struct gdy_ctx
     PersistCtl *ps_ctl = nullptr, *ps_ctl_host = nullptr;
     TraceRec *ps_trace_host = nullptr;
     uint32_t ps_epoch = 0;
-    uint32_t ps_seq = 0, ps_xseq = 0;
+    uint32_t ps_seq = 0, ps_xseq = 0, ps_xcount = 0;
+    uint32_t ps_repl_nact = 0;   // sharded runs: blocks this small are evaluated replicated (gdy_persist.cuh)
     bool ps_last = false;            // the last block step was done by the persistent kernel
     // peer-memory exchange of the persistent path (world > 1)
     bool peers_ok = false;
@@ -900,6 +901,8 @@ int run_persist(gdy_ctx *c, double itime, uint32_t nact, double t_stop, uint32_t
     a.epoch0 = c->ps_epoch;
     a.rank = c->rank; a.world = c->peers_ok ? c->world : 1;
     a.xseq0 = c->ps_xseq;
+    a.xcount0 = c->ps_xcount;
+    a.repl_nact = a.world > 1 ? c->ps_repl_nact : 0;
     for (int r = 0; r < PS_MAX_WORLD; ++r) a.xslot[r] = c->xslot[r];
     if (timed) CU(cudaEventRecord(c->ev0, c->st));
     void *args[] = {&a};
@@ -911,6 +914,9 @@ int run_persist(gdy_ctx *c, double itime, uint32_t nact, double t_stop, uint32_t
     if (c->ps_ctl_host->seq != a.seq) return fail(c, GDY_ERR_STATE, "persistent kernel left no result (seq %u != %u)", c->ps_ctl_host->seq, a.seq);
     c->ps_epoch = c->ps_ctl_host->epoch_end;
     c->ps_xseq += c->ps_ctl_host->steps;
+    if (a.world > 1)   // exchanges this launch did: every step whose block was not replicated (same count on every rank)
+        for (uint32_t k = 0; k < c->ps_ctl_host->steps; ++k)
+            if (c->ps_trace_host[k].nact > a.repl_nact) ++c->ps_xcount;
     c->ps_steps_total += c->ps_ctl_host->steps;
     if (ms_out)
     {
@@ -1003,6 +1009,10 @@ extern "C" int gdy_peer_attach(gdy_ctx *c, const uint8_t *handles)
     if (const char *e = getenv("GDY_PERSIST_NACT")) def = (uint32_t)atoi(e);
     if (def > (uint32_t)PS_NACT_CAP) def = PS_NACT_CAP;
     c->ps_nact_max = def;
+    // tiny blocks: one pass over all N on every rank beats a pass over N/world plus the exchange
+    // (measured per block step, N = 256k: profiles/r01_repl_small_steps_v10.md)
+    c->ps_repl_nact = PS_DEFAULT_REPL_NACT;
+    if (const char *e = getenv("GDY_REPL_NACT")) c->ps_repl_nact = (uint32_t)atoi(e);
     return GDY_OK;
 }
 

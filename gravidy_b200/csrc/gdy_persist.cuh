@@ -39,6 +39,7 @@ constexpr int PS_ICH = 64;             // active particles per i-chunk (32 i-lan
 constexpr int PS_NACT_CAP = 2048;      // hard cap of nact_max (partial buffer, shared lists)
 constexpr int PS_GMAX = 512;           // max CTAs (one flag / count per thread)
 constexpr int PS_MAX_WORLD = 8;
+constexpr int PS_DEFAULT_REPL_NACT = 16;   // sharded runs: blocks <= this are evaluated replicated, without exchange
 constexpr int PS_RREG = 4;             // scan rounds whose t+dt stay in registers
 constexpr int PS_NPROF = 16 + 2 * 64;   // 16 phase sums + two stamp rings (CTA 0, CTA G/2) of one step
 
@@ -83,6 +84,9 @@ struct PersistArgs
     // multi-GPU exchange through peer memory (world == 1: unused)
     int rank, world;
     uint32_t xseq0;            // exchange sequence number of the first step of this launch
+    uint32_t xcount0;          // exchanges done before this launch (their parity picks the slot buffer)
+    uint32_t repl_nact;        // world > 1: blocks of <= repl_nact active particles are evaluated against ALL N
+                               // j-particles on every rank (replicated, no exchange): cheaper than the exchange
     uint4 *xslot[PS_MAX_WORLD];       // rank r's exchange buffer (peer memory): [2][PS_MAX_WORLD][PS_NACT_CAP][6] flagged slots
 };
 
@@ -407,12 +411,13 @@ k_persist_steps(const PersistArgs a)
     uint32_t epoch = a.epoch0;
 
     // this CTA's slices: j-slice of the shard (force evaluation), scan slice of all N (scheduler)
-    const uint32_t nj = a.je - a.jb;
-    const uint32_t j0 = a.jb + (uint32_t)(((uint64_t)nj * cta) / G), j1 = a.jb + (uint32_t)(((uint64_t)nj * (cta + 1)) / G);
+    const uint32_t nj_sh = a.je - a.jb;
+    const uint32_t j0_sh = a.jb + (uint32_t)(((uint64_t)nj_sh * cta) / G), j1_sh = a.jb + (uint32_t)(((uint64_t)nj_sh * (cta + 1)) / G);
+    // ... and of ALL N, for the replicated tiny blocks of a sharded run (the same slices a one-GPU run uses)
+    const uint32_t j0_all = (uint32_t)(((uint64_t)a.n * cta) / G), j1_all = (uint32_t)(((uint64_t)a.n * (cta + 1)) / G);
     const uint32_t s0 = min(cta * a.slice, a.n), s1 = min(s0 + a.slice, a.n);
     const uint32_t rounds = (s1 - s0 + PS_T - 1) / PS_T;
-    const uint32_t njc = (j1 - j0 + PS_JCH - 1) / PS_JCH;
-    const bool restage = (nj + G - 1) / G > (uint32_t)PS_JCH;   // uniform over the grid
+    uint32_t nx = a.xcount0;   // exchanges so far: identical on every rank
 
     double itime = a.entry_itime;
     uint32_t nact = a.entry_nact;
@@ -440,6 +445,11 @@ k_persist_steps(const PersistArgs a)
     for (;;)
     {
         const uint32_t par = steps & 1u;
+        // uniform over the grid AND over the ranks (nact is replicated state)
+        const bool repl = a.world > 1 && nact <= a.repl_nact;
+        const uint32_t nj = repl ? a.n : nj_sh, j0 = repl ? j0_all : j0_sh, j1 = repl ? j1_all : j1_sh;
+        const uint32_t njc = (j1 - j0 + PS_JCH - 1) / PS_JCH;
+        const bool restage = (nj + G - 1) / G > (uint32_t)PS_JCH;
         GDY_STAMP(1);
         // ---- P1a: slice minimum of t+dt over the non-active particles and who attains it ----------------------
         // Short slices (<= 1024 particles): one warp does it alone, without CTA barriers, while the others already
@@ -628,14 +638,15 @@ k_persist_steps(const PersistArgs a)
                     double f[6];
 #pragma unroll
                     for (int c = 0; c < 6; ++c) f[c] = sm.fsum[pslot][c];
-                    if (a.world > 1)
+                    if (a.world > 1 && !repl)
                     {
                         // One-shot all-to-all over NVLink, fused into the step (this replaces ncclAllReduce, and
                         // the reference's host-side sum over GPUs, src/include/gpu/Hermite4GPU.cu:512-530): my
                         // shard's sum goes as flagged slots into buffer [parity][my rank][k] of EVERY rank (mine
                         // included); then the world sums are added in rank order, so every rank gets the same
-                        // bits.  Two parities: a rank can be at most one step ahead of the slowest reader.
-                        const uint32_t xp = tag & 1u;
+                        // bits.  Two parities: a rank can be at most one EXCHANGE ahead of the slowest reader (replicated
+                        // steps in between do not synchronise the ranks, so the parity counts exchanges, not steps).
+                        const uint32_t xp = nx & 1u;
                         double xv[2] = {0.0, 0.0};
 #pragma unroll
                         for (int u = 0; u < 2; ++u)
@@ -712,6 +723,7 @@ k_persist_steps(const PersistArgs a)
         last_itime = itime;
         last_nact = nact;
         ++steps;
+        if (a.world > 1 && !repl) ++nx;
         double cmin = INF;
         uint32_t ccnt = 0;
         uint2 head = make_uint2(0u, 0u);   // first two candidates of slice `tid`: most lists end there

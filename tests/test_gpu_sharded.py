@@ -56,10 +56,14 @@ def _two_gpu_available():
 
 
 @pytest.mark.skipif(not _two_gpu_available(), reason="needs 2 GPUs")
-@pytest.mark.parametrize("peers", [False, True])
-def test_two_real_shards_nccl(H, peers):
+@pytest.mark.parametrize("peers,repl", [(False, None), (True, 0), (True, 16)])
+def test_two_real_shards_nccl(H, peers, repl, monkeypatch):
     """peers = False: every block step through the per-hook kernels + ncclAllReduce.  peers = True: small
-    blocks through the persistent kernel with the fused NVLink exchange (peer memory), big ones as before."""
+    blocks through the persistent kernel with the fused NVLink exchange (peer memory), big ones as before;
+    repl = blocks of <= repl active particles are evaluated against all N on every rank, without exchange
+    (0: never), so exchanged and replicated steps alternate inside one launch."""
+    if repl is not None:
+        monkeypatch.setenv("GDY_REPL_NACT", str(repl))
     n, nsteps = 3000, 300 if peers else 60
     m, r, v = plummer(n, seed=8)
     single = H(m, r, v)

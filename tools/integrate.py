@@ -32,6 +32,7 @@ def main():
     ap.add_argument("--max-steps", type=int, default=0)
     ap.add_argument("--trace", type=int, default=400000)
     ap.add_argument("--out", default="")
+    ap.add_argument("--dump-trace", default="", help="npz of the per-step trace (nact, ITIME, us) of rank 0")
     ap.add_argument("--no-peers", action="store_true", help="sharded run without the fused NVLink exchange")
     a = ap.parse_args()
 
@@ -98,6 +99,8 @@ def main():
         "init_acc_jrk_s": t_init, "energy_s": t_energy, "launches": h.launch_count(), "bins": bins,
     }
     line["persist_launches"], line["persist_steps"] = h.persist_stats()
+    if rank == 0 and a.dump_trace:
+        np.savez_compressed(a.dump_trace, nact=tn, itime=ti, us=tu)
     if rank == 0:
         s = json.dumps(line)
         print(s, flush=True)
