@@ -67,3 +67,29 @@ def test_product_never_imports_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".cpp", ".hpp", ".h", ".mk")) or f == "Makefile":
                 txt = open(os.path.join(dp, f), errors="ignore").read()
                 assert not bad.search(txt), f"{os.path.join(dp, f)} reaches into oracle/"
+
+
+def test_force_kernel_fp64_instruction_budget():
+    """Codegen guard (no GPU): the inner loop of the big-block force kernel holds exactly 31 FP64-pipe instructions
+    per pair, 11 of them with three register sources, and ptxas still feeds some of those from the
+    operand reuse cache.  Read from the SASS of the built library with tools/sass_fp64_cost.py."""
+    import shutil
+    import sys
+    if not shutil.which("cuobjdump"):
+        pytest.skip("cuobjdump not on PATH")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    sys.path.insert(0, os.path.join(root, "tools"))
+    import sass_fp64_cost as S
+    from gravidy_b200 import capi
+    fns = S.functions(capi.LIB_PATH)
+    name = [k for k in fns if "k_force_warpILi2ELi4ELi1ELi3ELb0" in k]
+    assert len(name) == 1, name
+    seg = S.hottest_loop(fns[name[0]])
+    total, n64, n3, fed = S.cost(seg)
+    assert n64 % 31 == 0 and n64 >= 124, n64            # 31 per pair, >= 4 pairs per trip
+    pairs = n64 // 31
+    assert n3 == 11 * pairs, (n3, pairs)
+    assert fed >= 2 * pairs, (fed, pairs)
+    assert total / pairs < 72.6                          # below the nothing-fed bound
+    txt = "\n".join(i for _, i in fns[name[0]])
+    assert "UBLKCP" in txt and "MUFU.RSQ64H" in txt and "SYNCS" in txt   # TMA bulk copy, SFU seed, mbarrier
