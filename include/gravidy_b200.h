@@ -190,7 +190,10 @@ int gdy_persist_profile(gdy_ctx *ctx, uint64_t *ns_out /* [144] */);
  *   gdy_peer_export: handle of THIS context's exchange buffer (GDY_PEER_HANDLE_BYTES bytes);
  *   gdy_peer_attach: all `world` handles in rank order, gathered by the caller (MPI, torch.distributed,
  *                    a vector in the one-process-many-threads host program).  Same process: peer access;
- *                    other processes: CUDA IPC.  Switches the persistent path on for this shard. */
+ *                    other processes: CUDA IPC.  Switches the persistent path on for this shard.
+ * Blocks of <= 16 active particles (environment GDY_REPL_NACT at gdy_peer_attach, 0 = never) are not exchanged
+ * at all: every rank evaluates them against all N j-particles, as a one-GPU run would — one pass over N from L2
+ * costs less than a pass over N/world plus the NVLink round trip, and the ranks stay bit-identical. */
 #define GDY_PEER_HANDLE_BYTES 128
 int gdy_peer_export(gdy_ctx *ctx, uint8_t *handle_out);
 int gdy_peer_attach(gdy_ctx *ctx, const uint8_t *handles);
