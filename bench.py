@@ -33,7 +33,7 @@ sys.path.insert(0, ROOT)
 FLOP_PER_PAIR = 60.0
 METRIC = "hermite_fp64_gflops_60flop_per_pair_N256k"
 UNIT = "GFLOP/s"
-NCU_DRAM_BYTES_PER_LAUNCH = 16292608 + 2715392   # profiles/r01_force_warp_ncu_v9.md
+NCU_DRAM_BYTES_PER_LAUNCH = 14995712 + 2934272   # profiles/r01_force_warp_ncu_v12.md
 
 
 def parse_args():
@@ -370,9 +370,9 @@ def run_b200(args, m, r, v):
                          "traffic": NCU_DRAM_BYTES_PER_LAUNCH if (n == 262144 and world == 1) else None,
                          "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of one ncu --set full "
                                            "capture of this kernel at N=262144 on 1 GPU "
-                                           "(profiles/r01_force_warp_ncu_v9.md): 16.29 MB + 2.72 MB; "
+                                           "(profiles/r01_force_warp_ncu_v12.md): 15.00 MB + 2.93 MB; "
                                            "algorithmic 14.7 MB in + 12.6 MB out",
-                         "kernel": "k_force_warp<IPT=2,WI=4,WJ=1,NST=3>",
+                         "kernel": "k_force_warp<IPT=2,WI=1,WJ=4,NST=3> (warp_i64, 24 waves of CTAs)",
                          "peak_source": "DFMA micro-benchmark on this GPU (gdy_measure_fp64_peak); "
                                         "MEASURED_PEAKS.json has no FP64 entry",
                          "peak_equiv_sm_mhz_at_64_dfma_per_clk_per_sm": peak_mhz,

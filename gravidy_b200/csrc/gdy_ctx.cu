@@ -208,7 +208,7 @@ int alloc_all(gdy_ctx *c)
     const size_t np = c->npad;
     // 7 (r,m,v) + 6 f + 6 old + 3 a2 + 3 a3 + 2 (t,dt) + 7 pb + 6 fsum
     const size_t narr = 7 + 6 + 6 + 3 + 3 + 2 + 7 + 6;
-    c->part_cap = 6 * np > PART_MIN_DOUBLES ? 6 * np : PART_MIN_DOUBLES;
+    c->part_cap = 4 * 6 * np > PART_MIN_DOUBLES ? 4 * 6 * np : PART_MIN_DOUBLES;   // >= 4 j-splits at full-active
     c->pool_doubles = narr * np + c->part_cap;
     CU(cudaMalloc(&c->pool, c->pool_doubles * sizeof(double)));
     CU(cudaMemsetAsync(c->pool, 0, c->pool_doubles * sizeof(double), c->st));
@@ -541,8 +541,10 @@ int pick_variant(const gdy_ctx *c, uint32_t nact)
     // j across lanes straight from L2 has the lower fixed cost (no pipeline fill, no second launch);
     // it wins while the whole evaluation is a few tens of microseconds
     if (nact <= 160 || (uint64_t)nact * nj <= 12000000ull) return FV_LANE_I1x4;
-    if (nact <= 8192) return FV_WARP_I64;
-    return FV_WARP_I256;
+    // the smallest i-tile of the TMA-ring family at every size: with ~24 waves of small CTAs (plan_force) the
+    // block scheduler balances the SMs dynamically, and a CTA's prologue hides behind its neighbours' FP64 work
+    // (profiles/r01_sweep_split_v11.md: 517 vs 508 Gpairs/s for warp_i256 at full-active N = 256k)
+    return FV_WARP_I64;
 }
 
 // j-split: CTAs = i-tiles x splits run in waves of (SMs x resident CTAs); the cost of a plan is
@@ -571,6 +573,17 @@ ForcePlan plan_force(const gdy_ctx *c, uint32_t nact)
     }
     uint32_t split = 1;
     if (c->tune_jsplit > 0) split = (uint32_t)c->tune_jsplit;
+    else if (units > 1 && v.kind == 0)
+    {
+        // Warp kernels: many small CTAs.  Measured (tools/sweep_split.py, profiles/r01_sweep_split_v11.md): the rate
+        // keeps rising until ~20-28 waves of CTAs and down to ~16 j-blocks per CTA — the one-wave plans of the old
+        // wave model lost 2-8 % at awkward sizes (an SM that is a little slower, or has 3 CTAs instead of 4,
+        // decides the time), while per-CTA fixed costs overlap with the other resident CTAs' FP64 work.
+        split = cdiv(24u * slots, gx);
+        const uint32_t cap = units / 16 > 1 ? units / 16 : 1;
+        if (split > cap) split = cap;
+        if (split > 192) split = 192;
+    }
     else if (units > 1)
     {
         const uint64_t overhead = v.kind == 0 ? 3 : 2;   // per-CTA fixed cost in j-units

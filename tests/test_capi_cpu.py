@@ -82,14 +82,16 @@ def test_force_kernel_fp64_instruction_budget():
     import sass_fp64_cost as S
     from gravidy_b200 import capi
     fns = S.functions(capi.LIB_PATH)
-    name = [k for k in fns if "k_force_warpILi2ELi4ELi1ELi3ELb0" in k]
-    assert len(name) == 1, name
-    seg = S.hottest_loop(fns[name[0]])
-    total, n64, n3, fed = S.cost(seg)
-    assert n64 % 31 == 0 and n64 >= 124, n64            # 31 per pair, >= 4 pairs per trip
-    pairs = n64 // 31
-    assert n3 == 11 * pairs, (n3, pairs)
-    assert fed >= 2 * pairs, (fed, pairs)
-    assert total / pairs < 72.6                          # below the nothing-fed bound
-    txt = "\n".join(i for _, i in fns[name[0]])
-    assert "UBLKCP" in txt and "MUFU.RSQ64H" in txt and "SYNCS" in txt   # TMA bulk copy, SFU seed, mbarrier
+    # warp_i64 (IPT 2, WI 1, WJ 4: every block size of the TMA-ring range) and warp_i256 (WI 4, WJ 1)
+    for inst in ("k_force_warpILi2ELi1ELi4ELi3ELb0", "k_force_warpILi2ELi4ELi1ELi3ELb0"):
+        name = [k for k in fns if inst in k]
+        assert len(name) == 1, name
+        seg = S.hottest_loop(fns[name[0]])
+        total, n64, n3, fed = S.cost(seg)
+        assert n64 % 31 == 0 and n64 >= 124, n64            # 31 per pair, >= 4 pairs per trip
+        pairs = n64 // 31
+        assert n3 == 11 * pairs, (n3, pairs)
+        assert fed >= 2 * pairs, (fed, pairs)
+        assert total / pairs < 72.6                          # below the nothing-fed bound
+        txt = "\n".join(i for _, i in fns[name[0]])
+        assert "UBLKCP" in txt and "MUFU.RSQ64H" in txt and "SYNCS" in txt   # TMA bulk copy, SFU seed, mbarrier
