@@ -531,8 +531,7 @@ struct ForcePlan
 
 // Which kernel for how many active particles (set from tools/sweep_force.py on a B200, see
 // profiles/): small blocks put j across lanes and read it straight from L2; from a few hundred active
-// particles on, i sits in registers and j streams through the per-warp TMA rings, with the biggest
-// i-tile that still leaves every SM busy.
+// particles on, i sits in registers and j streams through the per-warp TMA rings.
 int pick_variant(const gdy_ctx *c, uint32_t nact)
 {
     if (c->tune_variant >= 0 && c->tune_variant < FV_COUNT) return c->tune_variant;
@@ -547,9 +546,9 @@ int pick_variant(const gdy_ctx *c, uint32_t nact)
     return FV_WARP_I64;
 }
 
-// j-split: CTAs = i-tiles x splits run in waves of (SMs x resident CTAs); the cost of a plan is
-// waves x (j-units per CTA + a fixed per-CTA overhead).  Minimising it fills the machine for small
-// blocks and avoids a ragged last wave for big ones.
+// j-split: CTAs = i-tiles x splits.  Lane kernels (latency-bound small blocks): the cost of a plan is
+// waves x (j-units per CTA + a fixed per-CTA overhead) with waves of (SMs x resident CTAs); minimising it
+// fills the machine.  Warp kernels: ~24 waves of small CTAs (see below).
 ForcePlan plan_force(const gdy_ctx *c, uint32_t nact)
 {
     ForcePlan p{};
