@@ -76,6 +76,7 @@ SIGNATURES = {
     "gdy_persist_profile": (C.c_int, [_ctx, C.POINTER(C.c_uint64)]),
     "gdy_measure_fp64_peak": (C.c_int, [_ctx, _dp, _dp]),
     "gdy_measure_copy_bw": (C.c_int, [_ctx, _dp]),
+    "gdy_plan_dry": (C.c_int, [C.c_uint32, C.c_uint32, C.c_int, C.c_int, C.c_int, C.c_int, _up]),
     "gdy_launch_count": (C.c_uint64, [_ctx]),
     "gdy_sync": (C.c_int, [_ctx]),
 }

@@ -203,12 +203,18 @@ constexpr size_t PART_MIN_DOUBLES = (size_t)8 << 20;   // 64 MiB of j-split part
 constexpr uint32_t PS_STEPS_MAX = 4096;                // block steps per persistent launch
 constexpr uint32_t PS_DEFAULT_NACT = 512;              // active sets up to this size go to the persistent kernel
 
+// doubles of j-split partial sums: 64 MiB at least, and room for >= 4 j-splits of a full-active sweep
+size_t part_cap_for(size_t np)
+{
+    return 4 * 6 * np > PART_MIN_DOUBLES ? 4 * 6 * np : PART_MIN_DOUBLES;
+}
+
 int alloc_all(gdy_ctx *c)
 {
     const size_t np = c->npad;
     // 7 (r,m,v) + 6 f + 6 old + 3 a2 + 3 a3 + 2 (t,dt) + 7 pb + 6 fsum
     const size_t narr = 7 + 6 + 6 + 3 + 3 + 2 + 7 + 6;
-    c->part_cap = 4 * 6 * np > PART_MIN_DOUBLES ? 4 * 6 * np : PART_MIN_DOUBLES;   // >= 4 j-splits at full-active
+    c->part_cap = part_cap_for(np);
     c->pool_doubles = narr * np + c->part_cap;
     CU(cudaMalloc(&c->pool, c->pool_doubles * sizeof(double)));
     CU(cudaMemsetAsync(c->pool, 0, c->pool_doubles * sizeof(double), c->st));
@@ -608,6 +614,32 @@ ForcePlan plan_force(const gdy_ctx *c, uint32_t nact)
     p.grid = dim3(gx, split, 1);
     return p;
 }
+
+}  // namespace
+
+// The launch plan of a force evaluation without touching a device (host logic only; tests/test_capi_cpu.py):
+// out = {variant, kind (0 warp / 1 lane), grid.x = i-tiles, grid.y = j-splits, j-units per split, first j-unit,
+// end j-unit, ld}; j-units are blocks of 64 particles for the warp kernels and particles for the lane kernels.
+extern "C" int gdy_plan_dry(uint32_t n, uint32_t nact, int rank, int world, int num_sms, int resident_ctas,
+                            uint32_t *out /* [8] */)
+{
+    if (!out || n == 0 || nact == 0 || nact > n || world < 1 || rank < 0 || rank >= world || num_sms < 1)
+        return GDY_ERR_INVALID;
+    gdy_ctx c;
+    c.n = n; c.npad = round_up(n, PAD); c.rank = rank; c.world = world;
+    const uint32_t nblk = c.npad / JB;
+    c.blk_begin = (uint32_t)((uint64_t)nblk * rank / world);
+    c.blk_end = (uint32_t)((uint64_t)nblk * (rank + 1) / world);
+    c.num_sms = num_sms;
+    for (int v = 0; v < FV_COUNT; ++v) c.occ[v] = resident_ctas > 0 ? resident_ctas : 4;
+    c.part_cap = part_cap_for(c.npad);
+    const ForcePlan p = plan_force(&c, nact);
+    out[0] = (uint32_t)p.variant; out[1] = (uint32_t)g_variants[p.variant].kind;
+    out[2] = p.grid.x; out[3] = p.grid.y; out[4] = p.per_split; out[5] = p.jb; out[6] = p.je; out[7] = p.ld;
+    return GDY_OK;
+}
+
+namespace {
 
 // Partial forces of `nact` i-particles (move == NULL: particles 0..nact-1) against this shard's
 // j-particles, summed over the j-splits and over the shards.  *out = k-indexed [6][ld] result buffer.

@@ -203,6 +203,13 @@ int gdy_peer_attach(gdy_ctx *ctx, const uint8_t *handles);
 int gdy_measure_fp64_peak(gdy_ctx *ctx, double *tflops_out, double *sm_mhz_out);
 int gdy_measure_copy_bw(gdy_ctx *ctx, double *gbs_out);
 
+/* The launch plan gdy_update_acc_jrk / gdy_init_acc_jrk would use for `nact` active particles of an n-particle
+ * shard (rank, world) on a GPU with num_sms SMs and resident_ctas force CTAs per SM (<= 0: 4), computed on the
+ * host without touching a device (tests: every j-unit of the shard is covered exactly once, the partial buffer
+ * holds all j-splits).  out[8] = {variant, kind 0 warp / 1 lane, i-tiles, j-splits, j-units per split, first
+ * j-unit, end j-unit, ld}; j-units = blocks of 64 particles (warp kernels) or particles (lane kernels). */
+int gdy_plan_dry(uint32_t n, uint32_t nact, int rank, int world, int num_sms, int resident_ctas, uint32_t *out);
+
 /* Number of kernels this context has launched (bench.py's gpu_launches). */
 uint64_t gdy_launch_count(const gdy_ctx *ctx);
 int gdy_sync(gdy_ctx *ctx);

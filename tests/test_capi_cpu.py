@@ -95,3 +95,48 @@ def test_force_kernel_fp64_instruction_budget():
         assert total / pairs < 72.6                          # below the nothing-fed bound
         txt = "\n".join(i for _, i in fns[name[0]])
         assert "UBLKCP" in txt and "MUFU.RSQ64H" in txt and "SYNCS" in txt   # TMA bulk copy, SFU seed, mbarrier
+
+
+@pytest.mark.parametrize("world", [1, 2, 3, 8])
+@pytest.mark.parametrize("n", [1, 63, 64, 65, 1000, 3001, 16384, 65536, 262144, 1048576])
+def test_force_plan_covers_the_shard_exactly_once(lib, n, world):
+    """Host logic of the force launch plan (gdy_plan_dry, no device): for ragged n / nact / shards the j-splits
+    tile the shard's j-units exactly once with no empty split, the i-tiles cover the active list, the j-split
+    partials fit their buffer, and big evaluations are cut into many waves of CTAs."""
+    out = (C.c_uint32 * 8)()
+    sms, occ = 148, 4
+    tile = {0: 256, 1: 128, 2: 64, 3: 32, 11: 512, 12: 128}
+    npad = -(-n // 256) * 256
+    part_cap = max(8 << 20, 24 * npad)
+    nacts = sorted({1, 2, 3, 33, 160, 161, 300, 1172, 10460, n // 2, n - 1, n} & set(range(1, n + 1)))
+    for rank in range(world):
+        lo, hi = C.c_uint32(), C.c_uint32()
+        assert lib.gdy_shard_range(n, rank, world, C.byref(lo), C.byref(hi)) == 0
+        for nact in nacts:
+            assert lib.gdy_plan_dry(n, nact, rank, world, sms, occ, out) == 0
+            variant, kind, gx, nsplit, per, jb, je, ld = list(out)
+            assert ld == -(-nact // 32) * 32
+            assert nsplit >= 1 and per >= 1
+            assert nsplit * 6 * ld <= part_cap, (n, nact, nsplit, ld)
+            if kind == 0:
+                assert gx == -(-nact // tile[variant]), (variant, gx, nact)
+                # blocks of 64: the shard's block range, also past n inside the padding (zero-mass particles)
+                assert jb * 64 <= lo.value or lo.value == hi.value
+                assert je * 64 >= hi.value
+                units = je - jb
+            else:
+                assert (jb, je) == (lo.value, hi.value) or lo.value == hi.value
+                units = je - jb
+            if units:
+                assert (nsplit - 1) * per < units <= nsplit * per, (n, nact, rank, units, nsplit, per)
+            if kind == 0 and world == 1 and units >= 16 * 192 and gx * 192 >= 24 * sms * occ:
+                assert gx * nsplit >= 20 * sms * occ, (n, nact, gx, nsplit)   # >= 20 waves of small CTAs
+
+
+def test_force_plan_rejects_bad_arguments(lib):
+    out = (C.c_uint32 * 8)()
+    assert lib.gdy_plan_dry(0, 1, 0, 1, 148, 4, out) != 0
+    assert lib.gdy_plan_dry(100, 0, 0, 1, 148, 4, out) != 0
+    assert lib.gdy_plan_dry(100, 101, 0, 1, 148, 4, out) != 0
+    assert lib.gdy_plan_dry(100, 10, 2, 2, 148, 4, out) != 0
+    assert lib.gdy_plan_dry(100, 10, 0, 1, 148, 4, None) != 0
