@@ -34,6 +34,8 @@ def main():
     ap.add_argument("--out", default="")
     ap.add_argument("--dump-trace", default="", help="npz of the per-step trace (nact, ITIME, us) of rank 0")
     ap.add_argument("--no-peers", action="store_true", help="sharded run without the fused NVLink exchange")
+    ap.add_argument("--rank-prof", default="", help="every rank writes its per-nact-bin step times and the persistent "
+                                                   "kernel's phase profile (GDY_PERSIST_PROF=1) to <prefix>.rank<r>.txt")
     a = ap.parse_args()
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -99,6 +101,16 @@ def main():
         "init_acc_jrk_s": t_init, "energy_s": t_energy, "launches": h.launch_count(), "bins": bins,
     }
     line["persist_launches"], line["persist_steps"] = h.persist_stats()
+    if a.rank_prof:
+        prof = h.persist_profile()
+        ps = max(line["persist_steps"], 1)
+        names = ["P1a", "P1b", "bar1", "P2", "bar2", "P3", "exit", "-", "b.stage", "b.sync", "b.pairs", "b.foldsync"]
+        with open(f"{a.rank_prof}.rank{rank}.txt", "w") as f:
+            f.write(f"rank {rank}/{world} wall {st.wall_ms:.1f} ms steps {st.iterations} persist_steps {ps}\n")
+            f.write("ns/step by phase (CTA 0): " + "  ".join(f"{nm} {v / ps:.0f}" for nm, v in zip(names, prof) if v) + "\n")
+            for b in bins:
+                f.write(f"nact ({b['nact'][0]},{b['nact'][1]}] steps {b['steps']} median_us {b['median_us']:.1f} "
+                        f"total_ms {b['share_of_wall'] * tu.sum() / 1e3:.2f}\n")
     if rank == 0 and a.dump_trace:
         np.savez_compressed(a.dump_trace, nact=tn, itime=ti, us=tu)
     if rank == 0:
