@@ -13,6 +13,13 @@ timed region.  Besides the contract's keys the JSON line carries
                 GFLOP/s and the extrapolated wall seconds per N-body time unit
   e2e           the same sweep through the C ABI with HOST buffers (upload r,v -> init_acc_jrk -> download
                 forces), copies inside the timed region
+  nbu           the second half of BASELINE.json's metric: the N = 256k block-timestep integration to t = 1 NBU,
+                wall seconds per N-body time unit, block steps, sum of nact, cumulative energy error
+  sweep_1m      the north-star target config: full-active sweep at N = 1 048 576, value and fraction of the FP64 peak
+  checks        what the numbers rest on, verified in this very run (rc != 0 when one fails): a subset of the forces
+                against the reference CPU code <= 1e-12; on several GPUs also: the forces after init_acc_jrk and the
+                state after the integration window hash to the same value on every rank, and the window's schedule
+                equals a one-GPU run of the same steps
 
 `--impl reference` times the reference CPU implementation alone (rank 0 only).
 """
@@ -49,7 +56,16 @@ def parse_args():
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--cpu-loop-steps", type=int, default=100,
                     help="block steps of the N-body loop the reference CPU code is timed on (cpu_baseline.loop)")
-    return ap.parse_args()
+    ap.add_argument("--no-nbu", action="store_true", help="skip the N=256k integration to t=1 (~100 s on one GPU)")
+    ap.add_argument("--nbu-tend", type=float, default=1.0)
+    ap.add_argument("--no-sweep-1m", action="store_true", help="skip the N=1M full-active sweep")
+    ap.add_argument("--no-checks", action="store_true")
+    ap.add_argument("--no-extras", action="store_true",
+                    help="only the timed sweep: no predictor/energy rooflines, e2e, integration, nbu, sweep_1m, checks")
+    a = ap.parse_args()
+    if a.no_extras:
+        a.no_integration = a.no_nbu = a.no_sweep_1m = a.no_checks = a.no_cpu_baseline = True
+    return a
 
 
 # ---- CPU arm ----------------------------------------------------------------------------------------------
@@ -154,6 +170,14 @@ class ClockSampler(threading.Thread):
 
 
 # ---- B200 arm ---------------------------------------------------------------------------------------------
+def _sha(*arrays):
+    import hashlib
+    hh = hashlib.sha256()
+    for a in arrays:
+        hh.update(np.ascontiguousarray(a).tobytes())
+    return hh.hexdigest()
+
+
 def run_b200(args, m, r, v):
     import torch
     import torch.distributed as dist
@@ -167,14 +191,8 @@ def run_b200(args, m, r, v):
                          "for the CPU arm)")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
-    uid = None
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
-        t = torch.zeros(128, dtype=torch.uint8, device=dev)
-        if rank == 0:
-            t.copy_(torch.frombuffer(bytearray(Hermite4B200.nccl_unique_id()), dtype=torch.uint8))
-        dist.broadcast(t, 0)
-        uid = bytes(t.cpu().numpy().tobytes())
 
     def barrier():
         torch.cuda.synchronize()
@@ -188,25 +206,66 @@ def run_b200(args, m, r, v):
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         return float(tt.item())
 
+    def gather(obj):
+        if world == 1:
+            return [obj]
+        out = [None] * world
+        dist.all_gather_object(out, obj)
+        return out
+
+    def make_ctx(mm, rr, vv):
+        """One j-shard per rank: NCCL communicator + peer memory for the fused NVLink exchanges."""
+        uid = None
+        if world > 1:
+            t = torch.zeros(128, dtype=torch.uint8, device=dev)
+            if rank == 0:
+                t.copy_(torch.frombuffer(bytearray(Hermite4B200.nccl_unique_id()), dtype=torch.uint8))
+            dist.broadcast(t, 0)
+            uid = bytes(t.cpu().numpy().tobytes())
+        hh = Hermite4B200(mm, rr, vv, softening=1e-4, eta=0.01, device=local, rank=rank, world=world, nccl_uid=uid)
+        if world > 1:
+            hh.peer_attach(gather(hh.peer_export()))
+            dist.barrier()
+        return hh
+
+    checks, failed = {}, []
+
+    def check(name, ok, detail=None):
+        checks[name] = {"ok": bool(ok), **({"detail": detail} if detail is not None else {})}
+        if not ok:
+            failed.append(name)
+
     n = len(m)
-    h = Hermite4B200(m, r, v, softening=1e-4, eta=0.01, device=local, rank=rank, world=world, nccl_uid=uid)
-    if world > 1:
-        # peer memory for the fused NVLink exchange of the persistent small-block kernel
-        hs = [None] * world
-        dist.all_gather_object(hs, h.peer_export())
-        h.peer_attach(hs)
-        dist.barrier()
+    h = make_ctx(m, r, v)
     h.init_acc_jrk()
     h.sync()
+    if not args.no_checks:
+        f6_init = h.download_forces()
+        hs = gather(_sha(f6_init))
+        check("forces_after_init_acc_jrk_identical_on_all_ranks", len(set(hs)) == 1, hs[0][:16])
+        if rank == 0:
+            # 64 particles of the same sweep by the reference's own update_acc_jrk (oracle/_ref, else the C port)
+            from oracle import oracle as O
+            o = O.best_oracle(m, r, v)
+            o.set_threads(os.cpu_count() or 1)
+            sub = np.sort(np.random.default_rng(99).choice(n, size=64, replace=False)).astype(np.uint32)
+            o.timed_update(sub)
+            fr = o.get_state("f6")["f6"][sub]
+            fg = f6_init[sub]
+            ea = float((np.linalg.norm(fg[:, :3] - fr[:, :3], axis=1) / np.linalg.norm(fr[:, :3], axis=1)).max())
+            ej = float((np.linalg.norm(fg[:, 3:] - fr[:, 3:], axis=1) / np.linalg.norm(fr[:, 3:], axis=1)).max())
+            check("forces_vs_reference_cpu_64_particles_le_1e-12", ea <= 1e-12 and ej <= 1e-12,
+                  {"acc_rel_err": ea, "jrk_rel_err": ej, "oracle": o.kind})
+            o.close()
     peak_tf, peak_mhz = h.measure_fp64_peak()
     pairs = float(n) * float(n)
 
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)   # > 126 MB L2
 
-    def one_step():
+    def one_step(hh=None):
         flush.zero_()
         barrier()
-        return h.force_sweep_full(1)
+        return (hh or h).force_sweep_full(1)
 
     for _ in range(args.warmup):
         one_step()
@@ -229,72 +288,97 @@ def run_b200(args, m, r, v):
     # the dominant kernel alone (rank-local j-shard, no allreduce): same number at 1 GPU
     kern_tf = (pairs / world) * FLOP_PER_PAIR / (float(np.mean(ms)) * 1e-3) / 1e12
 
-    # ---- the memory-bound kernel of the step: the predictor (120 B read + 48 B written per particle) ----
-    pred_ms = []
-    for _ in range(3 + 5):
-        flush.zero_()
-        torch.cuda.synchronize()
-        pred_ms.append(h.predict_timed(0.0))
-    pred_ms = float(np.mean(pred_ms[3:]))
     hbm_peak, hbm_src = 6551.4, "fallback: the B200 copy bandwidth of MEASURED_PEAKS.json on this pool (file absent)"
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
             hbm_peak, hbm_src = float(json.load(f)["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (copy, read+write bytes)"
     except Exception:
         pass
-    pred_gbs = 168.0 * n / (pred_ms * 1e-3) / 1e9
-    roofline_hbm = {"bound": "hbm", "kernel": "k_predict (predicted_pos_vel, all N, L2 flushed before each launch)",
-                    "achieved": pred_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": pred_gbs / hbm_peak,
-                    "us_per_launch": pred_ms * 1e3, "algorithmic_bytes_per_particle": 168, "traffic": None,
-                    "peak_source": hbm_src,
-                    "note": "one event-bracketed launch of ~10 us: launch latency is a third of it"}
-    # the same kernel where it is bandwidth-bound: N = 2M (352 MB per launch, nothing survives in the 126 MB L2),
-    # launches back to back — what the kernel sustains once launch latency is amortised
-    if rank == 0 and world == 1:
-        nb = 2097152
-        rng = np.random.default_rng(7)
-        hb = Hermite4B200(np.full(nb, 1.0 / nb), rng.standard_normal((nb, 3)), rng.standard_normal((nb, 3)),
-                          softening=1e-4, eta=0.01, device=local)
-        for _ in range(3):
-            hb.predict_timed(0.0)
-        reps = 20
-        torch.cuda.synchronize()
-        t0 = time.perf_counter()
-        big_ms = float(np.mean([hb.predict_timed(0.125 * (k + 1)) for k in range(reps)]))
-        big_wall = (time.perf_counter() - t0) / reps * 1e3
-        hb.close()
-        big_gbs = 168.0 * nb / (big_ms * 1e-3) / 1e9
-        roofline_hbm["bandwidth_regime"] = {"n": nb, "us_per_launch": big_ms * 1e3, "achieved": big_gbs,
-                                            "frac": big_gbs / hbm_peak, "wall_us_per_call": big_wall * 1e3,
-                                            "note": "same k_predict at N = 2M, working set 352 MB > L2, "
-                                                    "event-bracketed launches back to back"}
+    roofline_hbm = roofline_energy = None
+    if not args.no_extras:
+        # ---- the memory-bound kernel of the step: the predictor (120 B read + 48 B written per particle) ----
+        pred_ms = []
+        for _ in range(3 + 5):
+            flush.zero_()
+            torch.cuda.synchronize()
+            pred_ms.append(h.predict_timed(0.0))
+        pred_ms = float(np.mean(pred_ms[3:]))
+        pred_gbs = 168.0 * n / (pred_ms * 1e-3) / 1e9
+        roofline_hbm = {"bound": "hbm", "kernel": "k_predict (predicted_pos_vel, all N, L2 flushed before each launch)",
+                        "achieved": pred_gbs, "peak": hbm_peak, "unit": "GB/s", "frac": pred_gbs / hbm_peak,
+                        "us_per_launch": pred_ms * 1e3, "algorithmic_bytes_per_particle": 168, "traffic": None,
+                        "peak_source": hbm_src,
+                        "note": "one event-bracketed launch of ~10 us: launch latency is a third of it"}
+        # the same kernel where it is bandwidth-bound: N = 2M (352 MB per launch, nothing survives in the 126 MB L2),
+        # launches back to back — what the kernel sustains once launch latency is amortised
+        if rank == 0 and world == 1:
+            nb = 2097152
+            rng = np.random.default_rng(7)
+            hb = Hermite4B200(np.full(nb, 1.0 / nb), rng.standard_normal((nb, 3)), rng.standard_normal((nb, 3)),
+                              softening=1e-4, eta=0.01, device=local)
+            for _ in range(3):
+                hb.predict_timed(0.0)
+            reps = 20
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            big_ms = float(np.mean([hb.predict_timed(0.125 * (k + 1)) for k in range(reps)]))
+            big_wall = (time.perf_counter() - t0) / reps * 1e3
+            hb.close()
+            big_gbs = 168.0 * nb / (big_ms * 1e-3) / 1e9
+            roofline_hbm["bandwidth_regime"] = {"n": nb, "us_per_launch": big_ms * 1e3, "achieved": big_gbs,
+                                                "frac": big_gbs / hbm_peak, "wall_us_per_call": big_wall * 1e3,
+                                                "note": "same k_predict at N = 2M, working set 352 MB > L2, "
+                                                        "event-bracketed launches back to back"}
+        # ---- the other two FP64-bound kernels of SURVEY 8(d): energy and the k-th neighbour search ----------
+        if hasattr(h, "energy_timed"):
+            roofline_energy = {}
+            for nm, fn, instr in (("k_energy", h.energy_timed, 12.0), ("k_knn_distance", lambda: h.neighbour_timed(6), 9.0)):
+                fn()
+                tms = float(np.mean([fn() for _ in range(3)]))
+                # the FP64 pipe retires 64 lanes per clock per SM: instr / pair against the DFMA peak's instruction rate
+                ach = pairs / world * instr / (tms * 1e-3) / 1e12      # T(FP64 instr)/s
+                pk = peak_tf / 2.0                                      # the peak in DFMA instructions (2 flop each)
+                roofline_energy[nm] = {"bound": "fp64", "ms_per_launch": tms, "fp64_instr_per_ordered_pair": instr,
+                                       "achieved": ach, "peak": pk, "unit": "T FP64 instr/s", "frac": ach / pk,
+                                       "pairs_per_s": pairs / world / (tms * 1e-3),
+                                       "i_slice": f"rank's slice of {n // world} i-particles x all {n} j" if world > 1 else "all N x N"}
 
     # ---- e2e: host buffers through the C ABI, copies inside the timed region --------------------------
     r4 = torch.empty((n, 4), dtype=torch.float64).pin_memory().numpy()
     v4 = torch.empty((n, 4), dtype=torch.float64).pin_memory().numpy()
     f6 = torch.empty((n, 6), dtype=torch.float64).pin_memory().numpy()
     r4[:, :3] = r; r4[:, 3] = m; v4[:, :3] = v; v4[:, 3] = 0.0
+    e2e = None
+    if not args.no_extras:
+        # A sharded upload is collective: every rank is handed the same arrays, copies its own chunk over PCIe and the
+        # chunks are all-gathered over NVLink; the step's result is read back where it is wanted — on rank 0.
+        def e2e_step():
+            h.upload_particles(r4, v4)
+            h.init_acc_jrk()
+            if rank == 0:
+                h.download_forces(out=f6)
+            else:
+                h.sync()
 
-    def e2e_step():
-        h.upload_particles(r4, v4)
-        h.init_acc_jrk()
-        h.download_forces(out=f6)
-
-    for _ in range(2):
-        e2e_step()
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        e2e_step()
-    barrier()
-    e2e_s = max_over_ranks((time.perf_counter() - t0) / args.steps)
-    e2e = {"value": pairs / e2e_s * FLOP_PER_PAIR / 1e9, "unit": UNIT,
-           "h2d_bytes_per_step": int(r4.nbytes + v4.nbytes), "d2h_bytes_per_step": int(f6.nbytes),
-           "ms_per_step": e2e_s * 1e3,
-           "call": "gdy_upload_particles + gdy_init_acc_jrk + gdy_download_forces (pinned host buffers)"}
+        for _ in range(2):
+            e2e_step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            e2e_step()
+        barrier()
+        e2e_s = max_over_ranks((time.perf_counter() - t0) / args.steps)
+        e2e = {"value": pairs / e2e_s * FLOP_PER_PAIR / 1e9, "unit": UNIT,
+               "h2d_bytes_per_step": int(r4.nbytes + v4.nbytes),   # whole job: each rank copies 1/world of it
+               "d2h_bytes_per_step": int(f6.nbytes),
+               "ms_per_step": e2e_s * 1e3,
+               "call": "gdy_upload_particles + gdy_init_acc_jrk + gdy_download_forces (pinned host buffers)"
+                       + (f"; each rank uploads its 1/{world} of the particles and the chunks are all-gathered over NVLink, "
+                          "rank 0 downloads the forces" if world > 1 else "")}
 
     # ---- a window of the block-timestep integration (small active blocks) -----------------------------
     integ = None
+    loop_head = start = None
     if not args.no_integration:
         at = h.init_dt(0.0)
         want_cpu_loop = rank == 0 and world == 1 and not args.no_cpu_baseline and args.cpu_loop_steps > 0
@@ -305,11 +389,13 @@ def run_b200(args, m, r, v):
         barrier()
         loop_head = {"atime0": at, "nact": tn0, "us": tu0}
         l1 = h.launch_count()
+        x0 = h.exchange_stats()
         barrier()
         st, tn, _, tu = h.run(st.atime, 1e9, max_steps=args.integration_steps,
                               trace_cap=args.integration_steps, itime0=st.itime, trace_us=True)
         barrier()
         wall = max_over_ranks(st.wall_ms) * 1e-3
+        x1 = h.exchange_stats()
         integ = {"workload": f"block-timestep integration, Plummer N={n}, block steps {k0}..{k0 + st.iterations}",
                  "block_steps": int(st.iterations), "sum_nact": int(st.nsteps),
                  "mean_nact": float(st.nsteps) / max(int(st.iterations), 1),
@@ -318,7 +404,86 @@ def run_b200(args, m, r, v):
                  "us_per_block_step": wall / max(int(st.iterations), 1) * 1e6,
                  "gflops": st.interactions / wall * FLOP_PER_PAIR / 1e9,
                  "launches": h.launch_count() - l1, "t_reached": st.itime,
-                 "us_per_block_step_nact_le_32": float(np.median(tu[tn <= 32])) if (tn <= 32).any() else None}
+                 "us_per_block_step_nact_le_32": float(np.median(tu[tn <= 32])) if (tn <= 32).any() else None,
+                 "mean_us_per_block_step_nact_le_512": float(np.mean(tu[tn <= 512])) if (tn <= 512).any() else None,
+                 "exchanges_peer_memory": x1[0] - x0[0], "exchanges_nccl": x1[1] - x0[1]}
+        if not args.no_checks:
+            stt = h.get_state("r4", "v4", "f6", "t", "dt")
+            hs = gather(_sha(stt["r4"], stt["v4"], stt["f6"], stt["t"], stt["dt"]))
+            check("state_after_integration_window_identical_on_all_ranks", len(set(hs)) == 1, hs[0][:16])
+            if world > 1:
+                # the same block steps on ONE GPU (rank 0, a second context): the schedule must be the same
+                same = None
+                if rank == 0:
+                    h1 = Hermite4B200(m, r, v, softening=1e-4, eta=0.01, device=local)
+                    h1.init_acc_jrk()
+                    a1 = h1.init_dt(0.0)
+                    s1, t1a, _ = h1.run(a1, 1e9, max_steps=k0, trace_cap=k0)
+                    s1, t1b, _ = h1.run(s1.atime, 1e9, max_steps=args.integration_steps,
+                                        trace_cap=args.integration_steps, itime0=s1.itime)
+                    same = bool(np.array_equal(t1a, tn0) and np.array_equal(t1b, tn) and s1.itime == st.itime
+                                and s1.atime == st.atime)
+                    h1.close()
+                same = gather(same)[0]
+                check("window_schedule_equals_one_gpu_run", same)
+
+    # ---- the metric's second half: N = 256k integrated to t = 1 N-body time unit ---------------------------------
+    nbu = None
+    if not args.no_nbu:
+        h.upload_particles(r4, v4)
+        h.init_acc_jrk()
+        at = h.init_dt(0.0)
+        e0 = h.get_energy()
+        lb = h.launch_count()
+        x0 = h.exchange_stats()
+        p0 = h.persist_stats()
+        barrier()
+        st, tnn, _, tun = h.run(at, args.nbu_tend, trace_cap=400000, trace_us=True)
+        h.sync()
+        barrier()
+        wall = max_over_ranks(st.wall_ms) * 1e-3
+        e1 = h.get_energy()
+        x1 = h.exchange_stats()
+        p1 = h.persist_stats()
+        small = tnn <= 512
+        nbu = {"workload": f"Plummer N={n} equal mass, eps=1e-4, eta=0.01, block-timestep integration t=0..{args.nbu_tend:g} "
+                           f"through gdy_run (the reference's while loop, Hermite4CPU_integration.cpp:81-124)",
+               "wall_s": wall, "wall_s_per_nbu": wall / st.itime if st.itime > 0 else None, "t_reached": st.itime,
+               "block_steps": int(st.iterations), "sum_nact": int(st.nsteps), "pairs": int(st.interactions),
+               "gflops": st.interactions / wall * FLOP_PER_PAIR / 1e9,
+               "frac_fp64_peak": st.interactions / wall * FLOP_PER_PAIR / 1e12 / (peak_tf * world),
+               "e0": e0[0], "e1": e1[0], "cum_rel_energy_error": abs((e1[0] - e0[0]) / e0[0]),
+               "block_steps_le_512_active": int(small.sum()), "wall_s_in_block_steps_le_512_active": float(tun[small].sum()) * 1e-6,
+               "mean_us_per_block_step_le_512_active": float(tun[small].mean()) if small.any() else None,
+               "median_us_per_block_step_nact_le_32": float(np.median(tun[tnn <= 32])) if (tnn <= 32).any() else None,
+               "persistent_launches": p1[0] - p0[0], "persistent_block_steps": p1[1] - p0[1],
+               "launches": h.launch_count() - lb, "exchanges_peer_memory": x1[0] - x0[0], "exchanges_nccl": x1[1] - x0[1]}
+        if not args.no_checks:
+            es = gather((e0[0], e1[0], int(st.iterations), int(st.nsteps)))
+            check("nbu_energy_and_schedule_identical_on_all_ranks", len(set(es)) == 1)
+
+    # ---- the north-star target config: full-active sweep at N = 1M ------------------------------------------------
+    sweep_1m = None
+    if not args.no_sweep_1m:
+        from gravidy_b200.plummer import plummer, default_seed
+        n1 = 1048576
+        m1, r1, v1 = plummer(n1, seed=default_seed(n1))
+        h.close()
+        h = None
+        hm = make_ctx(m1, r1, v1)
+        hm.init_acc_jrk()
+        hm.sync()
+        one_step(hm)
+        ms1 = [one_step(hm) for _ in range(3)]
+        t1 = max_over_ranks(float(np.mean(ms1))) * 1e-3
+        g1 = float(n1) * n1 / t1 * FLOP_PER_PAIR / 1e9
+        sweep_1m = {"workload": f"full-active acc+jerk sweep, Plummer N={n1}, eps=1e-4, self pair counted, j-sharded x{world}",
+                    "ms_per_sweep": t1 * 1e3, "value": g1, "unit": UNIT, "frac_fp64_peak": g1 / 1e3 / (peak_tf * world),
+                    "reps": 3, "l2": "flushed between sweeps"}
+        if not args.no_checks and world > 1:
+            hs = gather(_sha(hm.download_forces()))
+            check("sweep_1m_forces_identical_on_all_ranks", len(set(hs)) == 1, hs[0][:16])
+        hm.close()
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -351,7 +516,14 @@ def run_b200(args, m, r, v):
                            "gpu_over_cpu_wall": cpu_wall / loop_head["gpu_wall_s"],
                            "schedule_identical": bool(np.array_equal(tno, loop_head["nact"][:k0])
                                                       and int(so.interactions) == loop_head["pairs"]),
-                           "kind": o.kind, "cores": info["cores"]}
+                           "kind": o.kind, "cores": info["cores"],
+                           "note": f"the ratio is against the {info['cores']} host cores of THIS box; a box with twice the cores halves it"}
+            if nbu is not None:
+                cpu["loop"]["nbu_extrapolated"] = {
+                    "cpu_wall_s": nbu["pairs"] / (so.interactions / cpu_wall), "gpu_wall_s": nbu["wall_s"],
+                    "gpu_over_cpu_wall": nbu["pairs"] / (so.interactions / cpu_wall) / nbu["wall_s"],
+                    "how": "the GPU run's pair count to t = 1 divided by the CPU loop's measured pairs/s"}
+            check("cpu_loop_schedule_identical", cpu["loop"]["schedule_identical"])
             o.close()
 
     if rank == 0:
@@ -378,15 +550,21 @@ def run_b200(args, m, r, v):
                          "peak_equiv_sm_mhz_at_64_dfma_per_clk_per_sm": peak_mhz,
                          "nominal_peak_at_max_clock": 2.0 * 64 * 148 * 1965e6 / 1e12,
                          "flop_convention": "60 flop/pair; the kernel issues 31 FP64 instructions/pair"},
-            "roofline_hbm": roofline_hbm,
+            "roofline_hbm": roofline_hbm, "roofline_energy": roofline_energy,
             "e2e": e2e, "gpu_launches": int(launches), "clocks": sampler.summary(),
-            "integration": integ, "cpu_baseline": cpu, "wall_timed_s": wall_timed,
+            "integration": integ, "nbu": nbu, "sweep_1m": sweep_1m,
+            "checks": {"ok": not failed, "failed": failed, "items": checks} if not args.no_checks else None,
+            "cpu_baseline": cpu, "wall_timed_s": wall_timed,
         }
         print(json.dumps(line), flush=True)
     barrier()
-    h.close()
+    if h is not None:
+        h.close()
     if world > 1:
         dist.destroy_process_group()
+    if failed:
+        sys.stderr.write("bench.py: CHECKS FAILED: " + ", ".join(failed) + "\n")
+        raise SystemExit(3)
 
 
 def main():

@@ -63,6 +63,8 @@ SIGNATURES = {
     "gdy_correction_pos_vel": (C.c_int, [_ctx, C.c_double, C.c_uint32]),
     "gdy_next_integration_time": (C.c_int, [_ctx, _dp]),
     "gdy_energy": (C.c_int, [_ctx, _dp, _dp]),
+    "gdy_energy_timed": (C.c_int, [_ctx, _dp, _dp, _fp]),
+    "gdy_neighbour_timed": (C.c_int, [_ctx, C.c_int, _fp]),
     "gdy_run": (C.c_int, [_ctx, C.c_double, C.c_double, C.c_double, C.c_uint64,
                           C.POINTER(RunStats), _up, _dp, _fp, C.c_uint64]),
     "gdy_force_sweep": (C.c_int, [_ctx, C.c_uint32, _up, _dp, _fp]),
@@ -78,6 +80,7 @@ SIGNATURES = {
     "gdy_measure_copy_bw": (C.c_int, [_ctx, _dp]),
     "gdy_plan_dry": (C.c_int, [C.c_uint32, C.c_uint32, C.c_int, C.c_int, C.c_int, C.c_int, _up]),
     "gdy_launch_count": (C.c_uint64, [_ctx]),
+    "gdy_exchange_stats": (C.c_int, [_ctx, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
     "gdy_sync": (C.c_int, [_ctx]),
 }
 

@@ -10,6 +10,7 @@
 #include "gdy_force.cuh"
 #include "gdy_step.cuh"
 #include "gdy_persist.cuh"
+#include "gdy_persist2.cuh"
 
 #include <chrono>
 #include <cmath>
@@ -35,6 +36,7 @@ struct NcclApi
     ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
     ncclResult_t (*AllReduce)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t,
                               cudaStream_t) = nullptr;
+    ncclResult_t (*AllGather)(const void *, void *, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
     const char *(*GetErrorString)(ncclResult_t) = nullptr;
     bool ok = false;
 };
@@ -58,6 +60,7 @@ bool nccl_load()
     GDY_SYM(CommInitRank, "ncclCommInitRank")
     GDY_SYM(CommDestroy, "ncclCommDestroy")
     GDY_SYM(AllReduce, "ncclAllReduce")
+    GDY_SYM(AllGather, "ncclAllGather")
     GDY_SYM(GetErrorString, "ncclGetErrorString")
 #undef GDY_SYM
     g_nccl.ok = true;
@@ -92,7 +95,7 @@ struct gdy_ctx
     double *d_stage = nullptr;       // AoS staging, npad*8 doubles
     size_t part_cap = 0;             // doubles in s.part
 
-    struct Pinned { SchedOut sched; double atime; double energy[2]; } *pin = nullptr;
+    struct Pinned { SchedOut sched; double atime; double energy[2]; uint32_t abort; } *pin = nullptr;
 
     uint32_t blk_begin = 0, blk_end = 0;     // this shard's j-blocks (units of JB = 64 particles)
     int num_sms = 148;
@@ -118,12 +121,25 @@ struct gdy_ctx
     uint32_t ps_seq = 0, ps_xseq = 0, ps_xcount = 0;
     uint32_t ps_repl_nact = 0;   // sharded runs: blocks this small are evaluated replicated (gdy_persist.cuh)
     bool ps_last = false;            // the last block step was done by the persistent kernel
+    // second design of the persistent kernel (gdy_persist2.cuh): flagged-slot buffers and the shared-memory carve-up
+    int ps_version = 2;              // GDY_PERSIST_V=1 selects the first design (grid barriers)
+    bool p2_ready = false;
+    uint4 *p2_ipub = nullptr, *p2_part = nullptr, *p2_anext = nullptr, *p2_cmin = nullptr;
+    uint2 *p2_ccnt = nullptr, *p2_clist = nullptr, *p2_ecnt = nullptr;
+    uint32_t *p2_abort = nullptr;
+    unsigned long long *p2_prof = nullptr;
+    uint32_t p2_off_dyn = 0, p2_lf_pad = 0, p2_res_cap = 0, p2_ls_cap = 0, p2_smem = 0;
+    unsigned long long spin_timeout_ns = 2000000000ull;   // watchdog of every in-kernel poll (GDY_SPIN_TIMEOUT_MS)
     // peer-memory exchange of the persistent path (world > 1)
     bool peers_ok = false;
     uint4 *xbuf = nullptr;           // my exchange buffer (peers store into it)
     uint4 *xslot[PS_MAX_WORLD] = {}; // every rank's buffer as seen from this device
     void *xopened[PS_MAX_WORLD] = {};// mappings opened with cudaIpcOpenMemHandle (other processes)
     uint64_t ps_steps_total = 0, ps_launches = 0;
+    uint32_t xmid_seq = 0;           // exchanges of the mid-block peer path so far (tag and slot parity)
+    bool sharded_upload = true;      // GDY_SHARDED_UPLOAD=0: every rank copies the whole particle set over PCIe
+    bool use_xmid = true;            // GDY_XMID=0: blocks above the persistent cap go through ncclAllReduce whatever their size
+    uint64_t xmid_count = 0, nccl_count = 0;
     char err[512] = "";
 };
 
@@ -163,6 +179,17 @@ inline uint32_t cdiv(uint32_t a, uint32_t b) { return (a + b - 1) / b; }
 inline uint32_t round_up(uint32_t a, uint32_t b) { return cdiv(a, b) * b; }
 
 int bind_device(gdy_ctx *c) { CU(cudaSetDevice(c->device)); return 0; }
+
+// the watchdog of the peer-memory exchange (k_xrecv / k_correct) reports through pinned memory; every call that
+// has just synchronised the stream looks at it
+int check_abort(gdy_ctx *c)
+{
+    if (c->pin && c->pin->abort)
+        return fail(c, GDY_ERR_STATE, "peer exchange watchdog: rank %d waited %.0f ms for a peer's partial forces "
+                    "(a peer rank died, was never attached or runs a different schedule); the state is undefined",
+                    c->rank, c->spin_timeout_ns * 1e-6);
+    return 0;
+}
 #define BIND(c) do { int r_ = bind_device(c); if (r_) return r_; } while (0)
 
 }  // namespace
@@ -200,6 +227,10 @@ extern "C" int gdy_nccl_unique_id(uint8_t *uid_out)
 namespace {
 
 constexpr size_t PART_MIN_DOUBLES = (size_t)8 << 20;   // 64 MiB of j-split partials at least
+// exchange buffer of a rank (peers store into it): the persistent kernel's slots, then the mid-block region
+constexpr size_t XBUF_SLOTS = (size_t)2 * PS_MAX_WORLD * PS_NACT_CAP * 6;
+constexpr size_t XMID_SLOTS = (size_t)2 * XMID_MAXW * 6 * XMID_LD;
+static_assert(XMID_MAXW == PS_MAX_WORLD, "one world limit");
 constexpr uint32_t PS_STEPS_MAX = 4096;                // block steps per persistent launch
 constexpr uint32_t PS_DEFAULT_NACT = 512;              // active sets up to this size go to the persistent kernel
 
@@ -247,7 +278,7 @@ int alloc_all(gdy_ctx *c)
     CU(cudaMalloc(&c->d_sched, sizeof(SchedOut)));
     CU(cudaMalloc(&c->d_atime, sizeof(double)));
     CU(cudaMalloc(&c->d_energy, 2 * sizeof(double)));
-    CU(cudaMalloc(&c->d_stage, np * 8 * sizeof(double)));
+    CU(cudaMalloc(&c->d_stage, (np + 64) * 8 * sizeof(double)));   // + room for the padded chunks of the sharded upload
     CU(cudaHostAlloc(&c->pin, sizeof(*c->pin), cudaHostAllocDefault));
     memset(c->pin, 0, sizeof(*c->pin));
 
@@ -273,7 +304,14 @@ int alloc_all(gdy_ctx *c)
         CU(cudaFuncSetAttribute((const void *)k_persist_steps<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PersistSmem)));
         CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, (const void *)k_persist_steps<false>, PS_T, sizeof(PersistSmem)));
         c->ps_grid = (uint32_t)c->num_sms;
+        // GDY_PS_GRID: fewer CTAs than SMs, so that two logical ranks can run their persistent kernels side by side
+        // on ONE device (tests of the peer-memory exchange on a single-GPU box)
+        if (const char *e = getenv("GDY_PS_GRID")) { const int g = atoi(e); if (g >= 1 && g <= c->num_sms) c->ps_grid = (uint32_t)g; }
         if (c->ps_grid > (uint32_t)PS_GMAX) c->ps_grid = PS_GMAX;
+        if (const char *e = getenv("GDY_PERSIST_V")) c->ps_version = atoi(e) == 1 ? 1 : 2;
+        if (const char *e = getenv("GDY_XMID")) c->use_xmid = atoi(e) != 0;
+        if (const char *e = getenv("GDY_SHARDED_UPLOAD")) c->sharded_upload = atoi(e) != 0;
+        if (const char *e = getenv("GDY_SPIN_TIMEOUT_MS")) { const long ms = atol(e); if (ms > 0) c->spin_timeout_ns = (unsigned long long)ms * 1000000ull; }
         c->ps_slice = round_up(cdiv(c->n, c->ps_grid), 2);   // even: the list heads are read as uint2
         c->ps_gpad = round_up(c->ps_grid, 32);
         CU(cudaMalloc(&c->ps_part, (size_t)PS_NACT_CAP * 6 * c->ps_gpad * sizeof(uint4)));
@@ -397,6 +435,8 @@ extern "C" int gdy_destroy(gdy_ctx *c)
     cudaFree(c->ps_part); cudaFree(c->ps_cta_min); cudaFree(c->ps_act_next); cudaFree(c->ps_cta_cnt);
     cudaFree(c->ps_cta_list); cudaFree(c->ps_flags); cudaFree(c->ps_exit_cnt); cudaFree(c->ps_ctl);
     cudaFree(c->ps_prof);
+    cudaFree(c->p2_ipub); cudaFree(c->p2_part); cudaFree(c->p2_anext); cudaFree(c->p2_cmin); cudaFree(c->p2_ccnt);
+    cudaFree(c->p2_clist); cudaFree(c->p2_ecnt); cudaFree(c->p2_abort); cudaFree(c->p2_prof);
     for (int r = 0; r < PS_MAX_WORLD; ++r)
         if (c->xopened[r]) cudaIpcCloseMemHandle(c->xopened[r]);
     cudaFree(c->xbuf);
@@ -433,7 +473,7 @@ int download_cols(gdy_ctx *c, double *host, int stride, int ncol, double *const 
     LAUNCHED(c);
     CU(cudaMemcpyAsync(host, c->d_stage, (size_t)c->n * stride * sizeof(double), cudaMemcpyDeviceToHost, c->st));
     CU(cudaStreamSynchronize(c->st));
-    return 0;
+    return check_abort(c);
 }
 
 }  // namespace
@@ -444,13 +484,39 @@ extern "C" int gdy_upload_particles(gdy_ctx *c, const double *r4, const double *
     if (!r4 || !v4) return fail(c, GDY_ERR_INVALID, "r4/v4 is NULL");
     BIND(c);
     State &s = c->s;
-    double *rc[4] = {s.x, s.y, s.z, s.m};
-    double *vc[4] = {s.vx, s.vy, s.vz, nullptr};
-    int r;
-    if ((r = upload_cols(c, r4, 4, 4, rc))) return r;
-    if ((r = upload_cols(c, v4, 4, 4, vc))) return r;
+    Cols rc{}, vc{};
+    rc.c[0] = s.x; rc.c[1] = s.y; rc.c[2] = s.z; rc.c[3] = s.m;
+    vc.c[0] = s.vx; vc.c[1] = s.vy; vc.c[2] = s.vz;
+    const size_t n = c->n;
+    if (c->world > 1 && c->comm && c->sharded_upload)
+    {
+        // A sharded run uploads collectively: every rank is handed the same full arrays (the state is replicated), so a
+        // rank copies only ITS chunk over PCIe and the chunks are all-gathered over NVLink (the reference pushes the
+        // whole set to every GPU through the host link: src/include/gpu/Hermite4GPU.cu:226-246).
+        const size_t chunk = cdiv(c->n, (uint32_t)c->world);
+        const size_t b = chunk * c->rank < n ? chunk * c->rank : n, e = b + chunk < n ? b + chunk : n;
+        double *mine = c->d_stage + (size_t)c->rank * chunk * 8;
+        if (e > b)
+        {
+            CU(cudaMemcpyAsync(mine, r4 + b * 4, (e - b) * 4 * sizeof(double), cudaMemcpyHostToDevice, c->st));
+            CU(cudaMemcpyAsync(mine + chunk * 4, v4 + b * 4, (e - b) * 4 * sizeof(double), cudaMemcpyHostToDevice, c->st));
+        }
+        NC(g_nccl.AllGather(mine, c->d_stage, chunk * 8, ncclDouble, c->comm, c->st));
+        k_unpack_chunks<<<cdiv(c->n, 256), 256, 0, c->st>>>(c->d_stage, rc, vc, (uint32_t)chunk, c->n);
+        LAUNCHED(c);
+    }
+    else
+    {
+        CU(cudaMemcpyAsync(c->d_stage, r4, n * 4 * sizeof(double), cudaMemcpyHostToDevice, c->st));
+        CU(cudaMemcpyAsync(c->d_stage + n * 4, v4, n * 4 * sizeof(double), cudaMemcpyHostToDevice, c->st));
+        k_unpack<<<cdiv(c->n, 256), 256, 0, c->st>>>(c->d_stage, rc, 4, 4, c->n);
+        LAUNCHED(c);
+        k_unpack<<<cdiv(c->n, 256), 256, 0, c->st>>>(c->d_stage + n * 4, vc, 4, 4, c->n);
+        LAUNCHED(c);
+    }
     k_init_pb<<<cdiv(c->npad, 256), 256, 0, c->st>>>(s, c->n, c->npad);   // mass row of the predicted set
     LAUNCHED(c);
+    CU(cudaStreamSynchronize(c->st));   // the host buffers are borrowed for the call only: ONE synchronisation
     c->have_particles = true;
     c->have_pred = false;
     return GDY_OK;
@@ -643,8 +709,12 @@ namespace {
 
 // Partial forces of `nact` i-particles (move == NULL: particles 0..nact-1) against this shard's
 // j-particles, summed over the j-splits and over the shards.  *out = k-indexed [6][ld] result buffer.
-int force_eval(gdy_ctx *c, uint32_t nact, const uint32_t *move, const double **out, uint32_t *ld_out, bool timed)
+// xr_out != NULL: where the ranks' sums travel through peer memory, the receive is left to the caller's corrector
+// (*xr_out filled in, base != NULL); otherwise *out holds the world's sums when this returns.
+int force_eval(gdy_ctx *c, uint32_t nact, const uint32_t *move, const double **out, uint32_t *ld_out, bool timed,
+               XRecv *xr_out = nullptr)
 {
+    if (xr_out) *xr_out = XRecv{};
     const State &s = c->s;
     const ForcePlan p = plan_force(c, nact);
     const ForceVariant &v = g_variants[p.variant];
@@ -666,8 +736,30 @@ int force_eval(gdy_ctx *c, uint32_t nact, const uint32_t *move, const double **o
     }
     else buf = s.part;
     if (timed) CU(cudaEventRecord(c->ev1, c->st));
-    if (c->world > 1 && c->comm)
+    if (c->world > 1 && c->peers_ok && c->use_xmid && nact <= (uint32_t)XMID_LD)
+    {
+        XSend xs{};
+        for (int r = 0; r < c->world; ++r) xs.peer[r] = c->xslot[r] + XBUF_SLOTS;
+        xs.rank = c->rank; xs.world = c->world; xs.tag = ++c->xmid_seq; xs.par = xs.tag & 1u;
+        k_xsend<<<cdiv(nact, 256), 256, 0, c->st>>>(buf, p.ld, nact, xs);
+        LAUNCHED(c);
+        XRecv xr{c->xbuf + XBUF_SLOTS, c->world, xs.tag, xs.par, &c->pin->abort, c->spin_timeout_ns};
+        ++c->xmid_count;
+        if (xr_out) *xr_out = xr;
+        else
+        {
+            k_xrecv<<<cdiv(nact, 256), 256, 0, c->st>>>(s.fsum, p.ld, nact, xr);
+            LAUNCHED(c);
+            buf = s.fsum;
+        }
+    }
+    else if (c->world > 1 && c->comm)
+    {
         NC(g_nccl.AllReduce(buf, buf, (size_t)6 * p.ld, ncclDouble, ncclSum, c->comm, c->st));
+        ++c->nccl_count;
+    }
+    else if (c->world > 1 && c->peers_ok)
+        return fail(c, GDY_ERR_STATE, "a block of %u active particles needs the NCCL communicator (peer exchange holds %d)", nact, (int)XMID_LD);
     *out = buf;
     *ld_out = p.ld;
     return 0;
@@ -787,6 +879,7 @@ extern "C" int gdy_find_particles_to_move(gdy_ctx *c, double itime, uint32_t *na
     int r;
     if ((r = launch_sched(c, itime, false))) return r;
     CU(cudaStreamSynchronize(c->st));
+    if ((r = check_abort(c))) return r;
     c->last_nact = c->pin->sched.nact;
     if (nact_out) *nact_out = c->last_nact;
     return GDY_OK;
@@ -857,7 +950,7 @@ extern "C" int gdy_correction_pos_vel(gdy_ctx *c, double itime, uint32_t nact)
     if (nact > c->n) return fail(c, GDY_ERR_INVALID, "nact %u > n %u", nact, c->n);
     BIND(c);
     if (nact == 0) return GDY_OK;
-    k_correct<<<cdiv(nact, 128), 128, 0, c->st>>>(c->s, nact, itime, (double)c->eta, nullptr, 0);
+    k_correct<<<cdiv(nact, 128), 128, 0, c->st>>>(c->s, nact, itime, (double)c->eta, nullptr, 0, XRecv{});
     LAUNCHED(c);
     return GDY_OK;
 }
@@ -875,49 +968,121 @@ extern "C" int gdy_next_integration_time(gdy_ctx *c, double *atime_out)
     return GDY_OK;
 }
 
+// get_energy_gpu(): the i-chunks (512 particles) are dealt to the shards in contiguous runs, every shard sums its chunks
+// over ALL j, the chunk sums travel in one allreduce whose other entries are zeros (x + 0 is exact, so every rank ends
+// up with every chunk sum bit for bit), and the total is a fixed-order tree over the chunks: the same bits on 1, 2, 4
+// or 8 GPUs (reference: i-slices per GPU, src/include/gpu/Hermite4GPU.cu:540-592).  A logical shard (world > 1 without a
+// communicator) returns the sum over its own chunks only.
+namespace {
+int energy_launch(gdy_ctx *c, float *ms_out)
+{
+    State &s = c->s;
+    const uint32_t nch_total = cdiv(c->n, EN_CHUNK), ntiles = c->npad / EN_TILE;
+    const uint32_t ch0 = (uint32_t)((uint64_t)nch_total * c->rank / c->world);
+    const uint32_t ch1 = (uint32_t)((uint64_t)nch_total * (c->rank + 1) / c->world);
+    // j-splits: a function of n alone (the decomposition must not depend on the number of GPUs): ~8 CTAs per SM-slot
+    uint32_t nsplit = cdiv(8u * 148u, nch_total);
+    if (nsplit > ntiles / 4) nsplit = ntiles / 4 ? ntiles / 4 : 1;
+    if (nsplit < 1) nsplit = 1;
+    const uint32_t per = cdiv(ntiles, nsplit);
+    nsplit = cdiv(ntiles, per);
+    double *cta_ek = s.part, *cta_ep = s.part + nch_total, *sums = cta_ep + (size_t)nsplit * nch_total;   // scratch
+    if ((size_t)(nsplit + 3) * nch_total > c->part_cap) return fail(c, GDY_ERR_STATE, "energy scratch too small");
+    if (ms_out) CU(cudaEventRecord(c->ev0, c->st));
+    if (ch1 > ch0)
+    {
+        k_energy<<<dim3(ch1 - ch0, nsplit), EN_T, 0, c->st>>>(s, c->n, ch0, per, ntiles, cta_ek, cta_ep, nch_total);
+        LAUNCHED(c);
+    }
+    if (ms_out) CU(cudaEventRecord(c->ev1, c->st));
+    k_energy_fold<<<cdiv(nch_total, 256), 256, 0, c->st>>>(cta_ek, cta_ep, nsplit, nch_total, ch0, ch1 - ch0, sums);
+    LAUNCHED(c);
+    if (c->world > 1 && c->comm)
+        NC(g_nccl.AllReduce(sums, sums, (size_t)2 * nch_total, ncclDouble, ncclSum, c->comm, c->st));
+    k_sum2<<<1, 1024, 0, c->st>>>(sums, sums + nch_total, nch_total, c->d_energy);
+    LAUNCHED(c);
+    CU(cudaMemcpyAsync(c->pin->energy, c->d_energy, 2 * sizeof(double), cudaMemcpyDeviceToHost, c->st));
+    CU(cudaStreamSynchronize(c->st));
+    if (ms_out) CU(cudaEventElapsedTime(ms_out, c->ev0, c->ev1));
+    return 0;
+}
+}  // namespace
+
 extern "C" int gdy_energy(gdy_ctx *c, double *ekin_out, double *epot_out)
 {
     if (!c) return GDY_ERR_INVALID;
     BIND(c);
     int r;
     if ((r = need_particles(c))) return r;
-    State &s = c->s;
-    // per-particle terms go to the (idle between steps) partial-force scratch
-    double *ek = s.part, *ep = s.part + c->npad;
-    k_energy<<<cdiv(c->n, 128), 128, 0, c->st>>>(s, c->n, c->npad, ek, ep);
-    LAUNCHED(c);
-    k_sum2<<<1, 1024, 0, c->st>>>(ek, ep, c->n, c->d_energy);
-    LAUNCHED(c);
-    CU(cudaMemcpyAsync(c->pin->energy, c->d_energy, 2 * sizeof(double), cudaMemcpyDeviceToHost, c->st));
-    CU(cudaStreamSynchronize(c->st));
+    if ((r = energy_launch(c, nullptr))) return r;
     if (ekin_out) *ekin_out = c->pin->energy[0];
     if (epot_out) *epot_out = c->pin->energy[1];
     return GDY_OK;
 }
 
-extern "C" int gdy_neighbour_distance(gdy_ctx *c, int k, double *dist_out)
+// the same with the pair kernel bracketed by CUDA events (bench: roofline of the FP64-bound energy kernel)
+extern "C" int gdy_energy_timed(gdy_ctx *c, double *ekin_out, double *epot_out, float *ms_out)
 {
-    if (!c) return GDY_ERR_INVALID;
-    if (k < 1 || k > KNN_MAX || !dist_out) return fail(c, GDY_ERR_INVALID, "k must be in [1, %d] and dist_out non-NULL", KNN_MAX);
+    if (!c || !ms_out) return GDY_ERR_INVALID;
     BIND(c);
     int r;
     if ((r = need_particles(c))) return r;
-    double *d = c->s.part;   // scratch
-    k_knn_distance<<<cdiv(c->n, 128), 128, 0, c->st>>>(c->s, c->n, c->npad, k, d);
-    LAUNCHED(c);
-    CU(cudaMemcpyAsync(dist_out, d, (size_t)c->n * sizeof(double), cudaMemcpyDeviceToHost, c->st));
-    CU(cudaStreamSynchronize(c->st));
+    if ((r = energy_launch(c, ms_out))) return r;
+    if (ekin_out) *ekin_out = c->pin->energy[0];
+    if (epot_out) *epot_out = c->pin->energy[1];
     return GDY_OK;
 }
 
+namespace {
+int knn_launch(gdy_ctx *c, int k, double *dist_out, float *ms_out)
+{
+    if (k < 1 || k > KNN_MAX) return fail(c, GDY_ERR_INVALID, "k must be in [1, %d]", KNN_MAX);
+    if (c->n <= (uint32_t)k) return fail(c, GDY_ERR_INVALID, "the %d-th neighbour needs more than %d particles (n = %u)", k, k, c->n);
+    int r;
+    if ((r = need_particles(c))) return r;
+    double *d = c->s.part;   // scratch
+    if (ms_out) CU(cudaEventRecord(c->ev0, c->st));
+    k_knn_distance<<<cdiv(c->n, KNN_T), KNN_T, 0, c->st>>>(c->s, c->n, c->npad, k, d);
+    LAUNCHED(c);
+    if (ms_out) CU(cudaEventRecord(c->ev1, c->st));
+    if (dist_out) CU(cudaMemcpyAsync(dist_out, d, (size_t)c->n * sizeof(double), cudaMemcpyDeviceToHost, c->st));
+    CU(cudaStreamSynchronize(c->st));
+    if (ms_out) CU(cudaEventElapsedTime(ms_out, c->ev0, c->ev1));
+    return 0;
+}
+}  // namespace
+
+extern "C" int gdy_neighbour_distance(gdy_ctx *c, int k, double *dist_out)
+{
+    if (!c) return GDY_ERR_INVALID;
+    if (!dist_out) return fail(c, GDY_ERR_INVALID, "dist_out is NULL");
+    BIND(c);
+    return knn_launch(c, k, dist_out, nullptr);
+}
+
+extern "C" int gdy_neighbour_timed(gdy_ctx *c, int k, float *ms_out)
+{
+    if (!c || !ms_out) return GDY_ERR_INVALID;
+    BIND(c);
+    return knn_launch(c, k, nullptr, ms_out);
+}
+
 extern "C" uint64_t gdy_launch_count(const gdy_ctx *c) { return c ? c->launches : 0; }
+
+extern "C" int gdy_exchange_stats(const gdy_ctx *c, uint64_t *peer_out, uint64_t *nccl_out)
+{
+    if (!c) return GDY_ERR_INVALID;
+    if (peer_out) *peer_out = c->xmid_count;
+    if (nccl_out) *nccl_out = c->nccl_count;
+    return GDY_OK;
+}
 
 extern "C" int gdy_sync(gdy_ctx *c)
 {
     if (!c) return GDY_ERR_INVALID;
     BIND(c);
     CU(cudaStreamSynchronize(c->st));
-    return GDY_OK;
+    return check_abort(c);
 }
 
 // ---- persistent small-step launches ------------------------------------------------------------------------
@@ -926,8 +1091,113 @@ namespace {
 // Runs block steps inside ONE cooperative launch while the active set stays <= ps_nact_max (see
 // gdy_persist.cuh).  Entry: ATIME = `itime` with its active list in State.move[0..nact).  Returns with
 // the pinned PersistCtl filled in; State.move then holds the list of the first step NOT done.
+// The second design needs its slices' t+dt and predicted set in shared memory; how much of the raw state stays
+// resident is what is left of the 227 KiB.  Returns GDY_OK with p2_ready == false when the slices do not fit
+// (very large N per GPU): those contexts keep to the launch-per-hook path for their small steps.
+int persist2_prepare(gdy_ctx *c)
+{
+    if (c->p2_ready || c->p2_smem == 1) return 0;
+    const uint32_t G = c->ps_grid;
+    uint32_t jb = c->blk_begin * JB, je = c->blk_end * JB < c->n ? c->blk_end * JB : c->n;
+    if (je < jb) je = jb;
+    const uint32_t lf = cdiv(je - jb, G) + 1, ls = cdiv(c->n, G) + 1;
+    int max_optin = 0;
+    CU(cudaDeviceGetAttribute(&max_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, c->device));
+    const size_t off = (sizeof(P2Fixed) + 15) & ~(size_t)15;
+    const uint32_t lf_pad = round_up(lf, 2), ls_cap = round_up(ls, 2);
+    const size_t need = off + (size_t)7 * lf_pad * 8 + (size_t)ls_cap * 8;
+    if (need > (size_t)max_optin) { c->p2_smem = 1; return 0; }   // does not fit: marked, not an error
+    uint32_t res = (uint32_t)(((size_t)max_optin - need) / (13 * 8));
+    if (res > lf_pad) res = lf_pad;
+    if (const char *e = getenv("GDY_P2_RESIDENT")) { const long r = atol(e); if (r >= 0 && (uint32_t)r < res) res = (uint32_t)r; }
+    c->p2_off_dyn = (uint32_t)off; c->p2_lf_pad = lf_pad; c->p2_ls_cap = ls_cap; c->p2_res_cap = res;
+    c->p2_smem = (uint32_t)(need + (size_t)13 * res * 8);
+    // the attribute belongs to the FUNCTION, not to this context: always the device maximum, so that contexts with
+    // different carve-ups (two logical ranks in one process) cannot shrink it under each other
+    CU(cudaFuncSetAttribute((const void *)k_persist2<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_optin));
+    CU(cudaFuncSetAttribute((const void *)k_persist2<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_optin));
+    int per_sm = 0;
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, (const void *)k_persist2<false>, PS_T, c->p2_smem));
+    if (per_sm < 1) { c->p2_smem = 1; return 0; }
+    const size_t gp = c->ps_gpad;
+    auto zalloc = [&](void **p, size_t bytes) -> cudaError_t {
+        cudaError_t e = cudaMalloc(p, bytes);
+        return e != cudaSuccess ? e : cudaMemsetAsync(*p, 0, bytes, c->st);
+    };
+    CU(zalloc((void **)&c->p2_ipub, (size_t)PS_NACT_CAP * 6 * sizeof(uint4)));
+    CU(zalloc((void **)&c->p2_part, (size_t)PS_NACT_CAP * 6 * gp * sizeof(uint4)));
+    CU(zalloc((void **)&c->p2_anext, (size_t)PS_NACT_CAP * sizeof(uint4)));
+    CU(zalloc((void **)&c->p2_cmin, 2 * gp * sizeof(uint4)));
+    CU(zalloc((void **)&c->p2_ccnt, 2 * gp * sizeof(uint2)));
+    CU(zalloc((void **)&c->p2_clist, (size_t)2 * G * PS_NACT_CAP * sizeof(uint2)));
+    CU(zalloc((void **)&c->p2_ecnt, gp * sizeof(uint2)));
+    CU(zalloc((void **)&c->p2_abort, sizeof(uint32_t)));
+    if (getenv("GDY_PERSIST_PROF")) CU(zalloc((void **)&c->p2_prof, P2_NPROF * sizeof(unsigned long long)));
+    CU(cudaStreamSynchronize(c->st));
+    c->p2_ready = true;
+    return 0;
+}
+
+int run_persist2(gdy_ctx *c, double itime, uint32_t nact, double t_stop, uint32_t budget, bool timed, float *ms_out)
+{
+    Persist2Args a{};
+    a.s = c->s; a.n = c->n;
+    a.jb = c->blk_begin * JB;
+    a.je = c->blk_end * JB < c->n ? c->blk_end * JB : c->n;
+    if (a.je < a.jb) a.je = a.jb;
+    a.e2 = c->e2; a.eta = (double)c->eta; a.t_stop = t_stop;
+    a.entry_itime = itime; a.entry_nact = nact;
+    a.max_steps = budget < PS_STEPS_MAX ? budget : PS_STEPS_MAX;
+    a.nact_max = c->ps_nact_max;
+    a.seq = ++c->ps_seq;
+    a.tag0 = c->ps_xseq;
+    a.ipub = c->p2_ipub; a.part = c->p2_part; a.anext = c->p2_anext; a.cmin = c->p2_cmin; a.ccnt = c->p2_ccnt;
+    a.clist = c->p2_clist; a.ecnt = c->p2_ecnt; a.gpad = c->ps_gpad; a.lcap = PS_NACT_CAP;
+    a.off_dyn = c->p2_off_dyn; a.lf_pad = c->p2_lf_pad; a.res_cap = c->p2_res_cap; a.ls_cap = c->p2_ls_cap;
+    a.ctl_dev = c->ps_ctl; a.ctl_host = c->ps_ctl_host; a.trace = c->ps_trace_host; a.prof = c->p2_prof;
+    a.abort_word = c->p2_abort; a.timeout_ns = c->spin_timeout_ns;
+    a.rank = c->rank; a.world = c->peers_ok ? c->world : 1;
+    for (int r = 0; r < PS_MAX_WORLD; ++r) a.xslot[r] = c->xslot[r];
+    if (timed) CU(cudaEventRecord(c->ev0, c->st));
+    void *args[] = {&a};
+    const void *fn = c->mask_self ? (const void *)k_persist2<true> : (const void *)k_persist2<false>;
+    {
+        cudaError_t le = cudaLaunchCooperativeKernel(fn, dim3(c->ps_grid), dim3(PS_T), args, c->p2_smem, c->st);
+        if (le != cudaSuccess)
+        {
+            int occ = -1;
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, PS_T, c->p2_smem);
+            return fail(c, GDY_ERR_CUDA, "cooperative launch of the persistent kernel: %s (grid %u x %d threads, %u B shared memory, "
+                        "%d resident CTAs per SM x %d SMs)", cudaGetErrorString(le), c->ps_grid, (int)PS_T, c->p2_smem, occ, c->num_sms);
+        }
+    }
+    ++c->launches; ++c->ps_launches;
+    if (timed) CU(cudaEventRecord(c->ev1, c->st));
+    CU(cudaStreamSynchronize(c->st));
+    if (c->ps_ctl_host->seq != a.seq) return fail(c, GDY_ERR_STATE, "persistent kernel left no result (seq %u != %u)", c->ps_ctl_host->seq, a.seq);
+    if (c->ps_ctl_host->epoch_end)
+    {
+        uint32_t ab = 0;
+        CU(cudaMemcpy(&ab, c->p2_abort, sizeof ab, cudaMemcpyDeviceToHost));
+        return fail(c, GDY_ERR_STATE, "persistent kernel watchdog: rank %d gave up after %.0f ms in phase %u of CTA %u at block step %u "
+                    "of the launch (a peer rank died, was never attached or runs a different schedule); the state is undefined",
+                    c->rank, c->spin_timeout_ns * 1e-6, ab ? (ab - 1) >> 16 : 0u, ab ? (ab - 1) & 0xffffu : 0u, c->ps_ctl_host->steps);
+    }
+    // tags: one per step, one for the exit exchange, and one more so that the next launch's first step has the other
+    // exchange-slot parity than this launch's last
+    c->ps_xseq += c->ps_ctl_host->steps + 2;
+    c->ps_steps_total += c->ps_ctl_host->steps;
+    if (ms_out)
+    {
+        *ms_out = 0.f;
+        if (timed) CU(cudaEventElapsedTime(ms_out, c->ev0, c->ev1));
+    }
+    return 0;
+}
+
 int run_persist(gdy_ctx *c, double itime, uint32_t nact, double t_stop, uint32_t budget, bool timed, float *ms_out)
 {
+    if (c->ps_version == 2 && c->p2_ready) return run_persist2(c, itime, nact, t_stop, budget, timed, ms_out);
     PersistArgs a{};
     a.s = c->s; a.n = c->n;
     a.jb = c->blk_begin * JB;
@@ -984,7 +1254,6 @@ extern "C" int gdy_set_persist(gdy_ctx *c, int nact_max)
 
 // ---- peer memory for the fused exchange of the persistent path ------------------------------------------------
 namespace {
-constexpr size_t XBUF_SLOTS = (size_t)2 * PS_MAX_WORLD * PS_NACT_CAP * 6;
 struct PeerHandle   // GDY_PEER_HANDLE_BYTES
 {
     uint64_t magic;
@@ -1003,8 +1272,8 @@ extern "C" int gdy_peer_export(gdy_ctx *c, uint8_t *handle_out)
     BIND(c);
     if (!c->xbuf)
     {
-        CU(cudaMalloc(&c->xbuf, XBUF_SLOTS * sizeof(uint4)));
-        CU(cudaMemset(c->xbuf, 0, XBUF_SLOTS * sizeof(uint4)));
+        CU(cudaMalloc(&c->xbuf, (XBUF_SLOTS + XMID_SLOTS) * sizeof(uint4)));
+        CU(cudaMemset(c->xbuf, 0, (XBUF_SLOTS + XMID_SLOTS) * sizeof(uint4)));
     }
     PeerHandle h{};
     h.magic = PEER_MAGIC; h.pid = (int32_t)getpid(); h.device = c->device; h.rank = c->rank; h.world = c->world;
@@ -1028,7 +1297,9 @@ extern "C" int gdy_peer_attach(gdy_ctx *c, const uint8_t *handles)
         if (h.magic != PEER_MAGIC || h.rank != r || h.world != c->world)
             return fail(c, GDY_ERR_INVALID, "peer handle %d is not rank %d of %d", r, r, c->world);
         if (r == c->rank) { c->xslot[r] = c->xbuf; continue; }
-        if (h.pid == (int32_t)getpid())
+        if (h.pid == (int32_t)getpid() && h.device == c->device)
+            c->xslot[r] = (uint4 *)(uintptr_t)h.ptr;   // two logical ranks on one device (tests): the same address space
+        else if (h.pid == (int32_t)getpid())
         {
             // same process (one thread per GPU): plain peer access to the other context's allocation
             int can = 0;
@@ -1066,6 +1337,12 @@ extern "C" int gdy_persist_profile(gdy_ctx *c, uint64_t *ns_out /* [PS_NPROF = 1
     if (!c || !ns_out) return GDY_ERR_INVALID;
     BIND(c);
     memset(ns_out, 0, PS_NPROF * sizeof(uint64_t));
+    if (c->ps_version == 2 && c->p2_prof)   // second design: P2_NPROF slots (tools/step_latency.py names them)
+    {
+        CU(cudaMemcpyAsync(ns_out, c->p2_prof, P2_NPROF * sizeof(uint64_t), cudaMemcpyDeviceToHost, c->st));
+        CU(cudaStreamSynchronize(c->st));
+        return GDY_OK;
+    }
     if (!c->ps_prof) return GDY_OK;
     CU(cudaMemcpyAsync(ns_out, c->ps_prof, PS_NPROF * sizeof(uint64_t), cudaMemcpyDeviceToHost, c->st));
     CU(cudaStreamSynchronize(c->st));
@@ -1109,7 +1386,8 @@ extern "C" int gdy_run(gdy_ctx *c, double atime, double itime0, double t_stop, u
     {
         if (max_steps && it >= max_steps) break;
         const uint32_t nact = c->pin->sched.nact;
-        if (c->ps_nact_max && nact && nact <= c->ps_nact_max)
+        if (c->ps_nact_max && c->ps_version == 2 && !c->p2_ready && c->p2_smem != 1 && (r = persist2_prepare(c))) return r;
+        if (c->ps_nact_max && nact && nact <= c->ps_nact_max && (c->ps_version == 1 || c->p2_ready))
         {
             // small active set: stay on the device until a big block (or t_stop / the step budget) comes up
             const uint64_t left = max_steps ? max_steps - it : PS_STEPS_MAX;
@@ -1162,8 +1440,9 @@ extern "C" int gdy_run(gdy_ctx *c, double atime, double itime0, double t_stop, u
         if (nact)
         {
             if ((r = launch_predict(c, ITIME, nact))) return r;
-            if ((r = force_eval(c, nact, s.move, &buf, &ld, timed))) return r;
-            k_correct<<<cdiv(nact, 128), 128, 0, c->st>>>(s, nact, ITIME, (double)c->eta, buf, ld);
+            XRecv xr;
+            if ((r = force_eval(c, nact, s.move, &buf, &ld, timed, &xr))) return r;
+            k_correct<<<cdiv(nact, 128), 128, 0, c->st>>>(s, nact, ITIME, (double)c->eta, buf, ld, xr);
             LAUNCHED(c);
         }
         if ((r = launch_min_time(c))) return r;
@@ -1174,6 +1453,7 @@ extern "C" int gdy_run(gdy_ctx *c, double atime, double itime0, double t_stop, u
         }
         else if ((r = launch_sched(c, 0.0, true))) return r;
         CU(cudaStreamSynchronize(c->st));
+        if ((r = check_abort(c))) return r;
         ATIME = last ? c->pin->atime : c->pin->sched.itime;
         if (timed && nact)
         {

@@ -171,7 +171,7 @@ __device__ __forceinline__ bool due_at(double itime, double tt) { return fabs(su
 // PS_T/IL; two i per thread (local k = il and IL + il).
 template <int IL, bool MASK>
 __device__ __forceinline__ void persist_pairs(const double *__restrict__ sj, int cnt, const double *si, double e2,
-                                              Acc6 &a0, Acc6 &a1)
+                                              Acc6 &a0, Acc6 &a1, const int JS = PS_JCH /* row stride of sj */)
 {
     constexpr int JL = PS_T / IL;
     const int il = threadIdx.x % IL, jl = threadIdx.x / IL;
@@ -182,9 +182,9 @@ __device__ __forceinline__ void persist_pairs(const double *__restrict__ sj, int
 #pragma unroll 2
     for (int j = jl; j < cnt; j += JL)
     {
-        const double xj = sj[j], yj = sj[PS_JCH + j], zj = sj[2 * PS_JCH + j];
-        const double uj = sj[3 * PS_JCH + j], vj = sj[4 * PS_JCH + j], wj = sj[5 * PS_JCH + j];
-        const double mj = sj[6 * PS_JCH + j];
+        const double xj = sj[j], yj = sj[JS + j], zj = sj[2 * JS + j];
+        const double uj = sj[3 * JS + j], vj = sj[4 * JS + j], wj = sj[5 * JS + j];
+        const double mj = sj[6 * JS + j];
         pair<MASK>(a0, x0, y0, z0, u0, v0, w0, xj, yj, zj, uj, vj, wj, mj, e2);
         pair<MASK>(a1, x1, y1, z1, u1, v1, w1, xj, yj, zj, uj, vj, wj, mj, e2);
     }
@@ -228,14 +228,14 @@ __device__ __forceinline__ void persist_fold(const Acc6 &a0, const Acc6 &a1, dou
 
 template <bool MASK>
 __device__ __forceinline__ void persist_pairs_fold(int IL, const double *sj, int cnt, const double *si, double e2,
-                                                   Acc6 &a0, Acc6 &a1, double *red, bool fold)
+                                                   Acc6 &a0, Acc6 &a1, double *red, bool fold, const int JS = PS_JCH)
 {
     switch (IL)
     {
 #define GDY_PS_CASE(n) \
-    case n: persist_pairs<n, MASK>(sj, cnt, si, e2, a0, a1); if (fold) persist_fold<n>(a0, a1, red); break;
+    case n: persist_pairs<n, MASK>(sj, cnt, si, e2, a0, a1, JS); if (fold) persist_fold<n>(a0, a1, red); break;
         GDY_PS_CASE(1) GDY_PS_CASE(2) GDY_PS_CASE(4) GDY_PS_CASE(8) GDY_PS_CASE(16)
-    default: persist_pairs<32, MASK>(sj, cnt, si, e2, a0, a1); if (fold) persist_fold<32>(a0, a1, red); break;
+    default: persist_pairs<32, MASK>(sj, cnt, si, e2, a0, a1, JS); if (fold) persist_fold<32>(a0, a1, red); break;
 #undef GDY_PS_CASE
     }
 }
@@ -256,7 +256,8 @@ struct PersistSmem
     uint32_t wcnt[PS_W];
 };
 
-__device__ __forceinline__ double block_min_ps(double m, PersistSmem &sm)
+template <class SM>
+__device__ __forceinline__ double block_min_ps(double m, SM &sm)
 {
 #pragma unroll
     for (int off = 16; off; off >>= 1) m = fmin(m, __shfl_xor_sync(0xffffffffu, m, off));
@@ -270,7 +271,8 @@ __device__ __forceinline__ double block_min_ps(double m, PersistSmem &sm)
 }
 
 // one round of an ordered block compaction: flags `on` in thread order -> out[running + rank]
-__device__ __forceinline__ void compact_round(bool on, uint32_t value, uint32_t *out, uint32_t &running, PersistSmem &sm)
+template <class SM>
+__device__ __forceinline__ void compact_round(bool on, uint32_t value, uint32_t *out, uint32_t &running, SM &sm)
 {
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const uint32_t bal = __ballot_sync(0xffffffffu, on);
@@ -285,7 +287,8 @@ __device__ __forceinline__ void compact_round(bool on, uint32_t value, uint32_t 
 }
 
 // exclusive block scan of one value per thread t < G into sm.cnt[0 .. G), total in sm.cnt[G]  (G <= PS_T)
-__device__ __forceinline__ uint32_t block_excl_scan(uint32_t c, uint32_t G, PersistSmem &sm)
+template <class SM>
+__device__ __forceinline__ uint32_t block_excl_scan(uint32_t c, uint32_t G, SM &sm)
 {
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     uint32_t incl = c;
@@ -703,7 +706,7 @@ k_persist_steps(const PersistArgs a)
                         for (int c = 0; c < 6; ++c) s.f[c][i] = f[c];
                         q.p = predict_raw(ri, itime);
                         store_pred(s, i, q.p);   // h_p of the active particles stays what the reference leaves there
-                        const double ndt = correct_core(s, i, itime, a.eta, q);
+                        const double ndt = correct_core(s, i, itime, a.eta, q).ndt;
                         a.act_next[k] = add(itime, ndt);
                         if (k == cta) GDY_STAMP(14);
                     }

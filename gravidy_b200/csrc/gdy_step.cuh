@@ -162,9 +162,10 @@ __device__ __forceinline__ double normalize_dt(double new_dt, double old_dt, dou
 // scatter at the end of update_acc_jrk and save_old_acc_jrk (reference: src/include/Hermite4.cpp:145-153)
 // fused into the corrector; same values, two launches fewer.
 // The arithmetic of one particle: old forces (oa, oj), new forces (fa, fj), old step dt1, predicted p.
-// Writes a2, a3, r, v, t, dt of particle i and returns the new step.
+// Writes a2, a3, r, v, t, dt of particle i and returns the corrected r, v and the new step.
 struct CorrIn { double dt1; double oa[3], oj[3], fa[3], fj[3]; Pred6 p; };
-__device__ __forceinline__ double correct_core(const State &s, uint32_t i, double itime, double eta, const CorrIn &q)
+struct CorrOut { double x, y, z, vx, vy, vz, ndt; };
+__device__ __forceinline__ CorrOut correct_core(const State &s, uint32_t i, double itime, double eta, const CorrIn &q)
 {
     const double dt1 = q.dt1;
     const double dt2 = mul(dt1, dt1);
@@ -201,12 +202,15 @@ __device__ __forceinline__ double correct_core(const State &s, uint32_t i, doubl
         s.a3[c][i] = a3[c];
     }
     // r = p.r + (dt4/24)*a2 + (dt5/120)*a3 ;  v = p.v + (dt3/6)*a2 + (dt4/24)*a3
-    s.x[i] = add(add(q.p.x, mul(c4_24, a2[0])), mul(c5_120, a3[0]));
-    s.y[i] = add(add(q.p.y, mul(c4_24, a2[1])), mul(c5_120, a3[1]));
-    s.z[i] = add(add(q.p.z, mul(c4_24, a2[2])), mul(c5_120, a3[2]));
-    s.vx[i] = add(add(q.p.vx, mul(c3_6, a2[0])), mul(c4_24, a3[0]));
-    s.vy[i] = add(add(q.p.vy, mul(c3_6, a2[1])), mul(c4_24, a3[1]));
-    s.vz[i] = add(add(q.p.vz, mul(c3_6, a2[2])), mul(c4_24, a3[2]));
+    CorrOut o;
+    o.x = add(add(q.p.x, mul(c4_24, a2[0])), mul(c5_120, a3[0]));
+    o.y = add(add(q.p.y, mul(c4_24, a2[1])), mul(c5_120, a3[1]));
+    o.z = add(add(q.p.z, mul(c4_24, a2[2])), mul(c5_120, a3[2]));
+    o.vx = add(add(q.p.vx, mul(c3_6, a2[0])), mul(c4_24, a3[0]));
+    o.vy = add(add(q.p.vy, mul(c3_6, a2[1])), mul(c4_24, a3[1]));
+    o.vz = add(add(q.p.vz, mul(c3_6, a2[2])), mul(c4_24, a3[2]));
+    s.x[i] = o.x; s.y[i] = o.y; s.z[i] = o.z;
+    s.vx[i] = o.vx; s.vy[i] = o.vy; s.vz[i] = o.vz;
     s.t[i] = itime;
 
     // get_timestep_normal(i, eta): h_dt[i] is still the old step here
@@ -221,13 +225,108 @@ __device__ __forceinline__ double correct_core(const State &s, uint32_t i, doubl
     const double abs_a1_22 = mul(abs_a1_2, abs_a1_2);
     const double normal_dt = __dsqrt_rn(
         mul(eta, dvd(add(mul(abs_a1, abs_a1_2), abs_j12), add(mul(abs_j1, abs_a1_3), abs_a1_22))));
-    const double ndt = normalize_dt(normal_dt, dt1, itime);
-    s.dt[i] = ndt;
-    return ndt;
+    o.ndt = normalize_dt(normal_dt, dt1, itime);
+    s.dt[i] = o.ndt;
+    return o;
+}
+
+// ---- one-shot exchange of the ranks' partial forces through peer memory (blocks of <= XMID_LD active particles) ----
+// Replaces ncclAllReduce (and the reference's host-side sum over GPUs, src/include/gpu/Hermite4GPU.cu:512-530) for
+// the blocks that are too big for the persistent kernel and too small for a bandwidth-optimal collective: k_xsend
+// stores this rank's sums as flagged 16-byte slots {lo, tag, hi, tag} into buffer [parity][my rank] of EVERY rank
+// over NVLink; the corrector of every rank polls its own buffer and adds the world's sums in rank order, so all
+// ranks correct with the same bits.  No barrier, no second collective kernel.  Two parities: a rank reaches the
+// send of exchange e+1 only behind its corrector of exchange e, which needed every rank's send of e, which they
+// issue (stream order) behind their corrector of e-1 — the last reader of the parity being rewritten.
+constexpr int XMID_LD = 16384;            // active particles per exchange at most
+constexpr int XMID_MAXW = 8;
+struct XRecv
+{
+    const uint4 *base;                    // my exchange buffer: [2][XMID_MAXW][6][XMID_LD] slots (NULL: fbuf holds the sums)
+    int world;
+    uint32_t tag, par;
+    uint32_t *abort_host;                 // pinned: set when a poll gives up
+    unsigned long long timeout_ns;
+};
+struct XSend
+{
+    uint4 *peer[XMID_MAXW];               // every rank's exchange buffer as seen from this device
+    int rank, world;
+    uint32_t tag, par;
+};
+
+__device__ __forceinline__ void xll_store_sys(uint4 *slot, double v, uint32_t tag)
+{
+    const unsigned long long b = (unsigned long long)__double_as_longlong(v);
+    asm volatile("st.relaxed.sys.global.v4.b32 [%0], {%1, %2, %3, %4};" ::"l"(slot), "r"((uint32_t)b), "r"(tag),
+                 "r"((uint32_t)(b >> 32)), "r"(tag)
+                 : "memory");
+}
+
+__global__ void __launch_bounds__(256)
+k_xsend(const double *__restrict__ fbuf, uint32_t ld, uint32_t nact, XSend x)
+{
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= nact) return;
+#pragma unroll
+    for (int c = 0; c < 6; ++c)
+    {
+        const double v = fbuf[(size_t)c * ld + k];
+        const size_t at = (((size_t)x.par * XMID_MAXW + x.rank) * 6 + c) * XMID_LD + k;
+        for (int r = 0; r < x.world; ++r) xll_store_sys(x.peer[r] + at, v, x.tag);
+    }
+}
+
+__device__ __forceinline__ double xrecv_sum(const XRecv &x, int c, uint32_t k)
+{
+    double sum = 0.0;
+    uint4 v[XMID_MAXW];
+    unsigned long long t0 = 0;
+    uint32_t spins = 0;
+    bool ok;
+    do {
+        ok = true;
+#pragma unroll
+        for (int r = 0; r < XMID_MAXW; ++r)
+            if (r < x.world)
+            {
+                const uint4 *p = x.base + (((size_t)x.par * XMID_MAXW + r) * 6 + c) * XMID_LD + k;
+                asm volatile("ld.relaxed.sys.global.v4.b32 {%0, %1, %2, %3}, [%4];"
+                             : "=r"(v[r].x), "=r"(v[r].y), "=r"(v[r].z), "=r"(v[r].w) : "l"(p) : "memory");
+                ok = ok && v[r].y == x.tag && v[r].w == x.tag;
+            }
+        if (!ok && (++spins & 255u) == 0)
+        {
+            unsigned long long t;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+            if (t0 == 0) t0 = t;
+            else if (t - t0 > x.timeout_ns || *(volatile uint32_t *)x.abort_host)
+            {
+                *(volatile uint32_t *)x.abort_host = 1u;   // the host fails the step (no reference behaviour to keep: it exits)
+                __threadfence_system();
+                return 0.0;
+            }
+        }
+    } while (!ok);
+#pragma unroll
+    for (int r = 0; r < XMID_MAXW; ++r)
+        if (r < x.world)
+            sum += __longlong_as_double((long long)(((unsigned long long)v[r].z << 32) | (unsigned long long)v[r].x));
+    return sum;
+}
+
+// the hook-by-hook path keeps update_acc_jrk and correction_pos_vel apart: the world's sums -> out[6][ld]
+__global__ void __launch_bounds__(256)
+k_xrecv(double *__restrict__ out, uint32_t ld, uint32_t nact, XRecv xr)
+{
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= nact) return;
+#pragma unroll
+    for (int c = 0; c < 6; ++c) out[(size_t)c * ld + k] = xrecv_sum(xr, c, k);
 }
 
 __global__ void k_correct(State s, uint32_t nact, double itime, double eta,
-                          const double *__restrict__ fbuf, uint32_t ld)
+                          const double *__restrict__ fbuf, uint32_t ld, XRecv xr)
 {
     const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= nact) return;
@@ -237,7 +336,16 @@ __global__ void k_correct(State s, uint32_t nact, double itime, double eta,
 #pragma unroll
     for (int c = 0; c < 3; ++c)
     {
-        if (fbuf)
+        if (xr.base)
+        {
+            q.oa[c] = s.f[c][i]; q.oj[c] = s.f[3 + c][i];
+            s.old[c][i] = q.oa[c]; s.old[3 + c][i] = q.oj[c];
+            q.fa[c] = xrecv_sum(xr, c, k);
+            q.fj[c] = xrecv_sum(xr, 3 + c, k);
+            s.f[c][i] = q.fa[c];
+            s.f[3 + c][i] = q.fj[c];
+        }
+        else if (fbuf)
         {
             q.oa[c] = s.f[c][i]; q.oj[c] = s.f[3 + c][i];
             s.old[c][i] = q.oa[c]; s.old[3 + c][i] = q.oj[c];
@@ -416,83 +524,162 @@ k_sched_write(State s, uint32_t n, double itime, const double *__restrict__ bloc
 // ---- energy ------------------------------------------------------------------------------------------
 // Kinetic 0.5 m v^2 and UNSOFTENED potential -sum_{i<j} m_i m_j / r_ij (reference:
 // src/include/utils/NbodyUtils.cpp:427-529; k_energy, src/include/gpu/Hermite4GPU_kernels.cu:250-288).
-// The reference's triangular j>i loop is load-imbalanced; here every i sums over all j != i on a
-// shared-memory tile and the result is halved.
-__global__ void __launch_bounds__(128)
-k_energy(State s, uint32_t n, uint32_t npad, double *__restrict__ ekin, double *__restrict__ epot)
+// The reference's triangular j>i loop is load-imbalanced; here every i sums over all j != i and the result is
+// halved.  A CTA of 256 threads holds EN_CHUNK = 512 i-particles (two per thread, in registers) and streams its
+// j-range through double-buffered shared-memory tiles of 256 particles (rows x y z m, read as broadcast LDS.128 = two
+// j per load): 12 FP64-pipe instructions + 1 compare per ordered pair.  Grid = (i-chunks of this rank, j-splits).
+// Every (chunk, split) sum is produced by one CTA in a fixed order and the chunk sums are added in chunk order, so
+// the energy has the same bits whatever the number of GPUs the chunks are spread over (reference: i-slices per GPU,
+// src/include/gpu/Hermite4GPU.cu:540-592).
+constexpr int EN_T = 256;
+constexpr int EN_CHUNK = 2 * EN_T;
+constexpr int EN_TILE = 256;
+
+__device__ __forceinline__ double block_sum_256(double v, double *sm /* [8] */)
 {
-    __shared__ double sx[128], sy[128], sz[128], smass[128];
-    const uint32_t i = blockIdx.x * 128 + threadIdx.x;
-    const uint32_t ic = i < n ? i : n - 1;
-    const double xi = s.x[ic], yi = s.y[ic], zi = s.z[ic];
-    double pot = 0.0;
-    for (uint32_t t = 0; t < npad; t += 128)
+#pragma unroll
+    for (int off = 16; off; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = v;
+    __syncthreads();
+    double t = sm[0];
+#pragma unroll
+    for (int w = 1; w < 8; ++w) t += sm[w];
+    return t;
+}
+
+__global__ void __launch_bounds__(EN_T)
+k_energy(State s, uint32_t n, uint32_t chunk0, uint32_t tiles_per_split, uint32_t ntiles,
+         double *__restrict__ cta_ek /* [nch] */, double *__restrict__ cta_ep /* [nsplit][nch_total] */, uint32_t nch_total)
+{
+    __shared__ __align__(16) double tile[2][4][EN_TILE];
+    __shared__ double red[8];
+    const int tid = threadIdx.x;
+    const uint32_t chunk = chunk0 + blockIdx.x;
+    const uint32_t i0 = chunk * EN_CHUNK + tid, i1 = i0 + EN_T;
+    const uint32_t c0 = i0 < n ? i0 : n - 1, c1 = i1 < n ? i1 : n - 1;
+    const double x0 = s.x[c0], y0 = s.y[c0], z0 = s.z[c0];
+    const double x1 = s.x[c1], y1 = s.y[c1], z1 = s.z[c1];
+    const uint32_t t0 = blockIdx.y * tiles_per_split, t1 = min(t0 + tiles_per_split, ntiles);
+    double p0 = 0.0, p1 = 0.0;
+    auto stage = [&](uint32_t t, int b) {
+        const uint32_t j = t * EN_TILE + tid;   // < npad: padding particles have zero mass and sit far away
+        tile[b][0][tid] = s.x[j]; tile[b][1][tid] = s.y[j]; tile[b][2][tid] = s.z[j]; tile[b][3][tid] = s.m[j];
+    };
+    if (t0 < t1) stage(t0, 0);
+    __syncthreads();
+    for (uint32_t t = t0; t < t1; ++t)
     {
-        __syncthreads();
-        sx[threadIdx.x] = s.x[t + threadIdx.x];
-        sy[threadIdx.x] = s.y[t + threadIdx.x];
-        sz[threadIdx.x] = s.z[t + threadIdx.x];
-        smass[threadIdx.x] = s.m[t + threadIdx.x];
-        __syncthreads();
+        const int b = (t - t0) & 1;
+        if (t + 1 < t1) stage(t + 1, b ^ 1);
 #pragma unroll 4
-        for (int j = 0; j < 128; ++j)
+        for (int j = 0; j < EN_TILE; j += 2)
         {
-            const double dx = sx[j] - xi, dy = sy[j] - yi, dz = sz[j] - zi;
-            const double r2 = fma(dz, dz, fma(dy, dy, dx * dx));
-            double y = rsqrt_f64(r2);
-            y = (r2 > 0.0) ? y : 0.0;   // i == j
-            pot = fma(smass[j], y, pot);
+            const double2 X = *reinterpret_cast<const double2 *>(&tile[b][0][j]);
+            const double2 Y = *reinterpret_cast<const double2 *>(&tile[b][1][j]);
+            const double2 Z = *reinterpret_cast<const double2 *>(&tile[b][2][j]);
+            const double2 M = *reinterpret_cast<const double2 *>(&tile[b][3][j]);
+#define GDY_EN_PAIR(xi, yi, zi, xj, yj, zj, mj, pot) \
+            { \
+                const double dx = xj - xi, dy = yj - yi, dz = zj - zi; \
+                const double r2 = fma(dz, dz, fma(dy, dy, dx * dx)); \
+                double y = rsqrt_f64(r2); \
+                y = (r2 > 0.0) ? y : 0.0;   /* i == j (and coincident particles: the reference gives inf there) */ \
+                pot = fma(mj, y, pot); \
+            }
+            GDY_EN_PAIR(x0, y0, z0, X.x, Y.x, Z.x, M.x, p0)
+            GDY_EN_PAIR(x1, y1, z1, X.x, Y.x, Z.x, M.x, p1)
+            GDY_EN_PAIR(x0, y0, z0, X.y, Y.y, Z.y, M.y, p0)
+            GDY_EN_PAIR(x1, y1, z1, X.y, Y.y, Z.y, M.y, p1)
+#undef GDY_EN_PAIR
         }
+        __syncthreads();
     }
-    if (i < n)
+    double ep = 0.0, ek = 0.0;
+    if (i0 < n) ep += -0.5 * s.m[i0] * p0;
+    if (i1 < n) ep += -0.5 * s.m[i1] * p1;
+    ep = block_sum_256(ep, red);
+    if (tid == 0) cta_ep[(size_t)blockIdx.y * nch_total + chunk] = ep;
+    if (blockIdx.y == 0)
     {
-        const double mi = s.m[i];
-        const double vx = s.vx[i], vy = s.vy[i], vz = s.vz[i];
-        ekin[i] = 0.5 * mi * (vx * vx + vy * vy + vz * vz);
-        epot[i] = -0.5 * mi * pot;
+        if (i0 < n) { const double vx = s.vx[i0], vy = s.vy[i0], vz = s.vz[i0]; ek += 0.5 * s.m[i0] * (vx * vx + vy * vy + vz * vz); }
+        if (i1 < n) { const double vx = s.vx[i1], vy = s.vy[i1], vz = s.vz[i1]; ek += 0.5 * s.m[i1] * (vx * vx + vy * vy + vz * vz); }
+        ek = block_sum_256(ek, red);
+        if (tid == 0) cta_ek[chunk] = ek;
     }
+}
+
+// chunk sums: the j-splits of a chunk in split order.  out = [2][nch_total]: kinetic, potential (chunks of other ranks: 0)
+__global__ void k_energy_fold(const double *__restrict__ cta_ek, const double *__restrict__ cta_ep, uint32_t nsplit,
+                              uint32_t nch_total, uint32_t chunk0, uint32_t nch, double *__restrict__ out)
+{
+    const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= nch_total) return;
+    double ek = 0.0, ep = 0.0;
+    if (c >= chunk0 && c < chunk0 + nch)
+    {
+        ek = cta_ek[c];
+        for (uint32_t sp = 0; sp < nsplit; ++sp) ep += cta_ep[(size_t)sp * nch_total + c];
+    }
+    out[c] = ek;
+    out[nch_total + c] = ep;
 }
 
 // ---- k-th nearest neighbour distance ------------------------------------------------------------------
 // The O(N^2) part of the Casertano & Hut density centre (reference: NbodyUtils::get_center_of_density,
-// src/include/utils/NbodyUtils.cpp:163-220, sorts all N distances of every particle on the host).
-// One thread per particle keeps the KNN_MAX smallest squared distances (self excluded) in registers,
-// j through shared-memory tiles.  Padding particles sit 1e10 away and never enter the list.
+// src/include/utils/NbodyUtils.cpp:163-220, sorts all N distances of every particle on the host and takes d[J],
+// the self entry 0 sorted first).  One thread per particle keeps the KNN_MAX smallest squared distances (self
+// excluded) in registers, j through double-buffered shared-memory tiles read as broadcast LDS.128.  r^2 is computed
+// WITHOUT contraction in the reference's order, (dx*dx + dy*dy) + dz*dz, so that sqrt of the k-th smallest r^2 has the
+// bits of the reference's d[k].  Padding particles sit 1e10 away and enter only when n <= k (refused by the host).
 constexpr int KNN_MAX = 8;
-__global__ void __launch_bounds__(128)
+constexpr int KNN_T = 128;
+__global__ void __launch_bounds__(KNN_T)
 k_knn_distance(State s, uint32_t n, uint32_t npad, int k, double *__restrict__ dist)
 {
-    __shared__ double sx[128], sy[128], sz[128];
-    const uint32_t i = blockIdx.x * 128 + threadIdx.x;
+    __shared__ __align__(16) double tile[2][3][KNN_T];
+    const int tid = threadIdx.x;
+    const uint32_t i = blockIdx.x * KNN_T + tid;
     const uint32_t ic = i < n ? i : n - 1;
     const double xi = s.x[ic], yi = s.y[ic], zi = s.z[ic];
     double best[KNN_MAX];
 #pragma unroll
     for (int q = 0; q < KNN_MAX; ++q) best[q] = 1e300;
-    for (uint32_t t = 0; t < npad; t += 128)
+    auto stage = [&](uint32_t t, int b) {
+        tile[b][0][tid] = s.x[t + tid]; tile[b][1][tid] = s.y[t + tid]; tile[b][2][tid] = s.z[t + tid];
+    };
+    stage(0, 0);
+    __syncthreads();
+    for (uint32_t t = 0; t < npad; t += KNN_T)
     {
-        __syncthreads();
-        sx[threadIdx.x] = s.x[t + threadIdx.x];
-        sy[threadIdx.x] = s.y[t + threadIdx.x];
-        sz[threadIdx.x] = s.z[t + threadIdx.x];
-        __syncthreads();
-        for (int j = 0; j < 128; ++j)
+        const int b = (t / KNN_T) & 1;
+        if (t + KNN_T < npad) stage(t + KNN_T, b ^ 1);
+#pragma unroll 2
+        for (int j = 0; j < KNN_T; j += 2)
         {
-            const double dx = sx[j] - xi, dy = sy[j] - yi, dz = sz[j] - zi;
-            double r2 = fma(dz, dz, fma(dy, dy, dx * dx));
-            if (t + j == ic) continue;            // self
-            if (r2 < best[KNN_MAX - 1])
-            {
-                // insertion into the sorted list (fully unrolled: stays in registers)
+            const double2 X = *reinterpret_cast<const double2 *>(&tile[b][0][j]);
+            const double2 Y = *reinterpret_cast<const double2 *>(&tile[b][1][j]);
+            const double2 Z = *reinterpret_cast<const double2 *>(&tile[b][2][j]);
 #pragma unroll
-                for (int q = 0; q < KNN_MAX; ++q)
+            for (int u = 0; u < 2; ++u)
+            {
+                const double dx = sub(u ? X.y : X.x, xi), dy = sub(u ? Y.y : Y.x, yi), dz = sub(u ? Z.y : Z.x, zi);
+                double r2 = add(add(mul(dx, dx), mul(dy, dy)), mul(dz, dz));
+                if (t + j + u == ic) r2 = 1e300;            // self
+                if (r2 < best[KNN_MAX - 1])
                 {
-                    const double lo = fmin(best[q], r2);
-                    r2 = fmax(best[q], r2);
-                    best[q] = lo;
+                    // insertion into the sorted list (fully unrolled: stays in registers)
+#pragma unroll
+                    for (int q = 0; q < KNN_MAX; ++q)
+                    {
+                        const double lo = fmin(best[q], r2);
+                        r2 = fmax(best[q], r2);
+                        best[q] = lo;
+                    }
                 }
             }
         }
+        __syncthreads();
     }
     if (i < n)
     {
@@ -528,6 +715,19 @@ __global__ void k_unpack(const double *__restrict__ aos, Cols cols, int ncol, in
     if (i >= n) return;
     for (int c = 0; c < ncol; ++c)
         if (cols.c[c]) cols.c[c][i] = aos[(size_t)i * stride + c];
+}
+// sharded upload: chunk r of the gather buffer holds `chunk` particles as [chunk][4] positions+mass, then [chunk][4]
+// velocities (gdy_upload_particles)
+__global__ void k_unpack_chunks(const double *__restrict__ g, Cols rc, Cols vc, uint32_t chunk, uint32_t n)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t rk = i / chunk, li = i % chunk;
+    const double *base = g + (size_t)rk * chunk * 8;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) rc.c[c][i] = base[(size_t)li * 4 + c];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) vc.c[c][i] = base[(size_t)chunk * 4 + (size_t)li * 4 + c];
 }
 __global__ void k_pack(double *__restrict__ aos, Cols cols, int ncol, int stride, uint32_t n)
 {

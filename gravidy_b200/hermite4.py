@@ -179,6 +179,17 @@ class Hermite4B200:
         self._ck(self.lib.gdy_energy(self.h, C.byref(ek), C.byref(ep)))
         return ek.value + ep.value, ek.value, ep.value
 
+    def energy_timed(self):
+        """get_energy with the pair kernel bracketed by CUDA events; returns its milliseconds."""
+        ek, ep, ms = C.c_double(), C.c_double(), C.c_float()
+        self._ck(self.lib.gdy_energy_timed(self.h, C.byref(ek), C.byref(ep), C.byref(ms)))
+        return ms.value
+
+    def neighbour_timed(self, k):
+        ms = C.c_float()
+        self._ck(self.lib.gdy_neighbour_timed(self.h, k, C.byref(ms)))
+        return ms.value
+
     def neighbour_distance(self, k):
         out = np.empty(self.n)
         self._ck(self.lib.gdy_neighbour_distance(self.h, k, _p(out)))
@@ -255,6 +266,12 @@ class Hermite4B200:
         gb = C.c_double()
         self._ck(self.lib.gdy_measure_copy_bw(self.h, C.byref(gb)))
         return gb.value
+
+    def exchange_stats(self):
+        """(force exchanges through peer memory, through ncclAllReduce) so far."""
+        a, b = C.c_uint64(), C.c_uint64()
+        self._ck(self.lib.gdy_exchange_stats(self.h, C.byref(a), C.byref(b)))
+        return a.value, b.value
 
     def launch_count(self):
         return int(self.lib.gdy_launch_count(self.h))

@@ -125,13 +125,21 @@ int gdy_correction_pos_vel(gdy_ctx *ctx, double itime, uint32_t nact);
 int gdy_next_integration_time(gdy_ctx *ctx, double *atime_out);
 
 /* get_energy_gpu() + k_energy (reference: Hermite4GPU.cu:540-592, Hermite4GPU_kernels.cu:250-288;
- * CPU: src/include/utils/NbodyUtils.cpp:427-529).  Unsoftened potential. */
+ * CPU: src/include/utils/NbodyUtils.cpp:427-529).  Unsoftened potential.  Sharded contexts with a communicator
+ * split the i-particles in chunks of 512 over the ranks (collective call) and all get the same bits as a one-GPU
+ * run; a sharded context WITHOUT a communicator returns the sum over its own chunks only. */
 int gdy_energy(gdy_ctx *ctx, double *ekin_out, double *epot_out);
+/* The same with the pair kernel bracketed by CUDA events (bench: FP64 roofline of k_energy). */
+int gdy_energy_timed(gdy_ctx *ctx, double *ekin_out, double *epot_out, float *ms_out);
 
 /* Distance of every particle to its k-th nearest neighbour (1 <= k <= 8) at the current positions:
  * the O(N^2) part of NbodyUtils::get_center_of_density (reference: src/include/utils/NbodyUtils.cpp:
- * 163-220, which sorts all N distances per particle on the host).  dist_out = n doubles. */
+ * 163-220, which sorts all N distances per particle on the host and takes d[J], the zero self entry sorted
+ * first).  dist_out = n doubles with the bits of the reference's d[k] (r^2 in the reference's operation order, no
+ * contraction, IEEE sqrt).  n <= k is GDY_ERR_INVALID. */
 int gdy_neighbour_distance(gdy_ctx *ctx, int k, double *dist_out);
+/* The same kernel bracketed by CUDA events, nothing downloaded (bench: FP64 roofline of k_knn_distance). */
+int gdy_neighbour_timed(gdy_ctx *ctx, int k, float *ms_out);
 
 /* ---- fused drivers (same arithmetic as the hooks, fewer launches / host round trips) -------------- */
 typedef struct gdy_run_stats
@@ -212,6 +220,9 @@ int gdy_plan_dry(uint32_t n, uint32_t nact, int rank, int world, int num_sms, in
 
 /* Number of kernels this context has launched (bench.py's gpu_launches). */
 uint64_t gdy_launch_count(const gdy_ctx *ctx);
+/* How many force exchanges between the shards went through peer memory (k_xsend + the corrector's flagged-slot
+ * receive, blocks of <= 16384 active particles once gdy_peer_attach has run) and how many through ncclAllReduce. */
+int gdy_exchange_stats(const gdy_ctx *ctx, uint64_t *peer_out, uint64_t *nccl_out);
 int gdy_sync(gdy_ctx *ctx);
 
 #ifdef __cplusplus

@@ -41,9 +41,10 @@ class RunStats(C.Structure):
 
 def build(force: bool = False) -> None:
     """Compile the checkers (``make -C oracle``).  Building the checker is not using it."""
-    if force or not os.path.exists(PORT_SO) or (
-        os.path.isdir("/root/reference/src") and not os.path.exists(REF_SO)
-    ):
+    src_new = os.path.isdir("/root/reference/src") and (
+        not os.path.exists(REF_SO)
+        or os.path.getmtime(os.path.join(HERE, "ref_harness.cpp")) > os.path.getmtime(REF_SO))
+    if force or not os.path.exists(PORT_SO) or src_new:
         subprocess.run(["make", "-C", HERE], check=True, stdout=subprocess.DEVNULL)
 
 
@@ -256,6 +257,21 @@ class RefOracle(_Base):
 
     def normalize_dt(self, new_dt, old_dt, t):
         return self.lib.gref_normalize_dt(self.h, new_dt, old_dt, t)
+
+    def center_of_density(self):
+        """NbodyUtils::get_center_of_density of the reference, single-threaded (its OpenMP loop races on shared
+        temporaries).  Returns (x, y, z); J = self.J neighbours."""
+        self.lib.gref_center_of_density.argtypes = [C.c_void_p, _dp]
+        prev = self.lib.gref_max_threads()
+        self.set_threads(1)
+        out = np.zeros(3)
+        self.lib.gref_center_of_density(self.h, _ptr(out, _dp))
+        self.set_threads(prev)
+        return out
+
+    @property
+    def J(self):
+        return int(self.lib.gref_J())
 
     def set_print_options(self, print_all=False, print_lagrange=False):
         self.lib.gref_set_print_options.argtypes = [C.c_void_p, C.c_int, C.c_int]

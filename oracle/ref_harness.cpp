@@ -129,6 +129,16 @@ double gref_normalize_dt(gref *g, double new_dt, double old_dt, double t)
     return g->nu->normalize_dt(new_dt, old_dt, t, 0);
 }
 
+// NbodyUtils::get_center_of_density (reference: src/include/utils/NbodyUtils.cpp:163-220): N sorts of N distances,
+// density from the J-th neighbour (J = 6, common.hpp:96), float accumulators.  The reference's OpenMP loop shares
+// radius/aa/bb between threads: call it with ONE thread (gref_set_threads(1)) for a defined result.
+void gref_center_of_density(gref *g, double *out3)
+{
+    double3 c = g->nu->get_center_of_density();
+    out3[0] = c.x; out3[1] = c.y; out3[2] = c.z;
+}
+int gref_J(void) { return J; }
+
 // The reference's own driver, unmodified: writes <prefix>.out.{info,log,snapshot_*}.
 void gref_integration(gref *g) { g->h4->integration(); }
 

@@ -252,6 +252,68 @@ def test_energy_vs_oracle(H, O):
     np.testing.assert_allclose(h.get_energy(), o.get_energy(), rtol=1e-12)
 
 
+@pytest.mark.parametrize("n", [640, 5000])
+@pytest.mark.parametrize("world", [2, 3, 8])
+def test_energy_of_logical_shards_adds_up(H, n, world):
+    """i-chunks of 512 particles dealt to the shards: the shards' sums add up to the one-GPU energy (a sharded context
+    without a communicator returns the sum over its own chunks)."""
+    m, r, v = plummer(n, seed=22, mass_spectrum="salpeter")
+    full = H(m, r, v)
+    e, ek, ep = full.get_energy()
+    sk = sp = 0.0
+    for rank in range(world):
+        h = H(m, r, v, rank=rank, world=world, nccl_uid=None)
+        _, k1, p1 = h.get_energy()
+        sk += k1; sp += p1
+        h.close()
+    assert abs(sk - ek) <= 4e-16 * abs(ek) * world and abs(sp - ep) <= 4e-16 * abs(ep) * world
+
+
+# ---- density centre: the J-th neighbour search (SURVEY 8f.1) -------------------------------------------
+def _kth_neighbour_numpy(r, k):
+    """sqrt of the k-th smallest squared distance, self excluded; r^2 in the reference's operation order
+    (rx*rx + ry*ry) + rz*rz without contraction (reference: src/include/utils/NbodyUtils.cpp:189-192)."""
+    out = np.empty(len(r))
+    for i in range(len(r)):
+        d = r - r[i]
+        d2 = (d[:, 0] * d[:, 0] + d[:, 1] * d[:, 1]) + d[:, 2] * d[:, 2]
+        d2[i] = np.inf
+        out[i] = np.sqrt(np.partition(d2, k - 1)[k - 1])
+    return out
+
+
+def _density_centre(m, r, dist, J):
+    """The tail of NbodyUtils::get_center_of_density with the reference's float temporaries
+    (reference: src/include/utils/NbodyUtils.cpp:166-168, 198-219)."""
+    radius = dist.astype(np.float32).astype(np.float64)
+    aa = ((J - 1) * m).astype(np.float32)
+    bb = ((4.0 * np.pi * radius * radius * radius) / 3.0).astype(np.float32)
+    p = (aa / bb).astype(np.float64)                  # float / float, stored in a double
+    dsum = np.float32(0.0)
+    for x in p:                                       # float accumulator
+        dsum = np.float32(np.float64(dsum) + x)
+    return (r * p[:, None]).sum(axis=0) / np.float64(dsum)
+
+
+@pytest.mark.parametrize("n", [257, 4099])
+def test_neighbour_distance_vs_reference(H, O, n):
+    m, r, v = plummer(n, seed=31, mass_spectrum="salpeter" if n == 257 else "equal")
+    h = H(m, r, v)
+    for k in (1, 6, 8):
+        got = h.neighbour_distance(k)
+        assert np.array_equal(got, _kth_neighbour_numpy(r, k)), k     # bit-equal to the exact ordering
+    if not O.have_ref():
+        pytest.skip("oracle/_ref not built")
+    o = O.RefOracle(m, r, v)
+    assert o.J == 6                                                   # reference: src/include/common.hpp:96
+    ref = o.center_of_density()                                       # the reference's own function, one thread
+    got = _density_centre(m, r, h.neighbour_distance(o.J), o.J)
+    scale = np.abs(r).max()
+    assert np.abs(got - ref).max() <= 1e-6 * scale, (got, ref)
+    with pytest.raises(Exception):
+        H(m[:6], r[:6], v[:6]).neighbour_distance(6)                  # n <= k: refused, not padded
+
+
 # ---- size-independent properties at BASELINE sizes -----------------------------------------------------
 @pytest.mark.parametrize("n", [65536, 262144])
 def test_full_size_properties(H, O, n):

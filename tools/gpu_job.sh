@@ -1,0 +1,77 @@
+#!/bin/bash
+# One parameterised GPU job: `gpurun [--gpus N] -- 'bash tools/gpu_job.sh TAG stage [stage ...]'`.
+# Every stage writes gpurun_out/<TAG>_<stage>.{log,json,...}; a stage is `name` or `name:arg1:arg2`.
+#
+#   tests            pytest -m gpu (whole suite)                 tests:<file-or-k-expr>  a subset
+#   bench[:N]        bench.py on N GPUs (default 1)               benchref  bench.py --impl reference
+#   lat:<n>[:spec]   tools/step_latency.py at n particles         integ:<n>:<tend>[:gpus[:extra env]]  tools/integrate.py
+#   ncu_force        ncu --set full of the force kernel in bench.py (one capture) + launch list
+#   sanit            compute-sanitizer memcheck + racecheck of a short persistent-kernel run
+#   diag4            the 4-GPU small-step diagnostic of round 2 (phase profile of every rank)
+set -u
+TAG=$1; shift
+O=gpurun_out
+mkdir -p $O
+export PYTHONUNBUFFERED=1
+TR() { np=$1; shift; python -m torch.distributed.run --nnodes=1 --nproc-per-node $np --master-addr 127.0.0.1 --master-port $((29500 + np)) "$@"; }
+for st in "$@"; do
+  IFS=: read -r name a1 a2 a3 a4 <<< "$st"
+  t0=$(date +%s)
+  case $name in
+    tests)
+      if [ -z "${a1:-}" ]; then timeout 1500 python -m pytest tests -m gpu -x -q > $O/${TAG}_tests.log 2>&1
+      elif [ -f "tests/$a1" ]; then timeout 1500 python -m pytest tests/$a1 -m gpu -x -q > $O/${TAG}_tests.log 2>&1
+      else timeout 1500 python -m pytest tests -m gpu -x -q -k "$a1" > $O/${TAG}_tests.log 2>&1; fi
+      echo "[$st] rc=$? $(tail -1 $O/${TAG}_tests.log)";;
+    bench)
+      g=${a1:-1}
+      if [ "$g" = 1 ]; then timeout 1500 python bench.py ${a2:-} > $O/${TAG}_bench_1gpu.json 2> $O/${TAG}_bench_1gpu.err
+      else timeout 1500 bash -c "$(declare -f TR); TR $g bench.py --gpus $g ${a2:-}" > $O/${TAG}_bench_${g}gpu.json 2> $O/${TAG}_bench_${g}gpu.err; fi
+      echo "[$st] rc=$? $(tail -c 600 $O/${TAG}_bench_${g}gpu.json)";;
+    benchref)
+      timeout 900 python bench.py --impl reference > $O/${TAG}_bench_reference.json 2> $O/${TAG}_bench_reference.err
+      echo "[$st] rc=$? $(tail -c 300 $O/${TAG}_bench_reference.json)";;
+    lat)
+      GDY_PERSIST_PROF=1 timeout 600 python tools/step_latency.py --n $a1 --spectrum ${a2:-equal} ${a3:+--steps $a3} > $O/${TAG}_lat_n$a1.txt 2>&1
+      echo "[$st] rc=$?"; head -30 $O/${TAG}_lat_n$a1.txt;;
+    integ)
+      g=${a3:-1}
+      if [ "$g" = 1 ]; then env ${a4:-X=1} timeout 900 python tools/integrate.py --particles $a1 --tend $a2 --rank-prof $O/${TAG}_integ_n${a1}_${g}gpu > $O/${TAG}_integ_n${a1}_${g}gpu.json 2> $O/${TAG}_integ_n${a1}_${g}gpu.err
+      else env ${a4:-X=1} timeout 900 bash -c "$(declare -f TR); TR $g tools/integrate.py --particles $a1 --tend $a2 --rank-prof $O/${TAG}_integ_n${a1}_${g}gpu" > $O/${TAG}_integ_n${a1}_${g}gpu.json 2> $O/${TAG}_integ_n${a1}_${g}gpu.err; fi
+      echo "[$st] rc=$? $(python - <<PY
+import json
+try:
+    d = json.loads(open("$O/${TAG}_integ_n${a1}_${g}gpu.json").read().strip().splitlines()[-1])
+    print("wall", round(d["wall_s"], 4), "steps", d["block_steps"], "E", d["cum_rel_energy_error"], "persist", d["persist_steps"],
+          " ".join("%s:%.1f" % (b["nact"][1], b["median_us"]) for b in d["bins"]))
+except Exception as e:
+    print("no result:", e)
+PY
+)";;
+    ncu_force)
+      timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_force_warp -c 1 -o $O/${TAG}_force_warp \
+        python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-integration --no-extras > $O/${TAG}_ncu_force.log 2>&1
+      echo "[$st] rc=$?"
+      timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/${TAG}_launches.csv \
+        python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-extras > $O/${TAG}_ncu_launches.log 2>&1
+      echo "[$st] launches rc=$?";;
+    sanit)
+      timeout 1200 compute-sanitizer --tool memcheck --error-exitcode 9 python tools/sanitize_smoke.py > $O/${TAG}_sanit_memcheck.log 2>&1
+      echo "[$st] memcheck rc=$? $(tail -2 $O/${TAG}_sanit_memcheck.log | tr '\n' ' ')"
+      GDY_SANIT_SHORT=1 timeout 1200 compute-sanitizer --tool racecheck --error-exitcode 9 python tools/sanitize_smoke.py > $O/${TAG}_sanit_racecheck.log 2>&1
+      echo "[$st] racecheck rc=$? $(tail -2 $O/${TAG}_sanit_racecheck.log | tr '\n' ' ')";;
+    diag4)
+      export GDY_PERSIST_PROF=1
+      T=0.0078125
+      timeout 300 python tools/integrate.py --particles 262144 --tend $T --rank-prof $O/${TAG}_diag_1gpu > $O/${TAG}_diag_1gpu.json 2> $O/${TAG}_diag_1gpu.err
+      timeout 300 bash -c "$(declare -f TR); TR 4 tools/integrate.py --particles 262144 --tend $T --rank-prof $O/${TAG}_diag_4gpu_default" > $O/${TAG}_diag_4gpu_default.json 2> $O/${TAG}_diag_4gpu_default.err
+      GDY_REPL_NACT=2048 timeout 300 bash -c "$(declare -f TR); TR 4 tools/integrate.py --particles 262144 --tend $T --rank-prof $O/${TAG}_diag_4gpu_repl" > $O/${TAG}_diag_4gpu_repl.json 2> $O/${TAG}_diag_4gpu_repl.err
+      for g in 0 1 2 3; do
+        CUDA_VISIBLE_DEVICES=$g timeout 300 python tools/integrate.py --particles 262144 --tend $T --rank-prof $O/${TAG}_diag_indep$g > $O/${TAG}_diag_indep$g.json 2> $O/${TAG}_diag_indep$g.err &
+      done
+      wait; unset GDY_PERSIST_PROF
+      tail -n 30 $O/${TAG}_diag_*.txt;;
+    *) echo "unknown stage $st";;
+  esac
+  echo "[$st] $(( $(date +%s) - t0 )) s"
+done

@@ -105,6 +105,9 @@ def main():
         prof = h.persist_profile()
         ps = max(line["persist_steps"], 1)
         names = ["P1a", "P1b", "bar1", "P2", "bar2", "P3", "exit", "-", "b.stage", "b.sync", "b.pairs", "b.foldsync"]
+        if os.environ.get("GDY_PERSIST_V", "2") != "1":
+            names = ["load", "A.publish", "B.predict+scan", "P1.wait_i", "P1.pairs+publish", "P2", "P3.wait", "P3.lists",
+                     "exit", "-", "-", "-", "xchg.wait_total", "xchg.count"]
         with open(f"{a.rank_prof}.rank{rank}.txt", "w") as f:
             f.write(f"rank {rank}/{world} wall {st.wall_ms:.1f} ms steps {st.iterations} persist_steps {ps}\n")
             f.write("ns/step by phase (CTA 0): " + "  ".join(f"{nm} {v / ps:.0f}" for nm, v in zip(names, prof) if v) + "\n")

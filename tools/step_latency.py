@@ -29,7 +29,11 @@ if a.dump:
 pl, ps = h.persist_stats()
 prof = h.persist_profile()
 print(f"  persistent kernel: {pl} launches, {ps} block steps ({ps / max(pl, 1):.1f} per launch)")
-if any(prof):
+if any(prof) and os.environ.get("GDY_PERSIST_V", "2") != "1":
+    names = ["load", "A.publish", "B.predict+scan", "P1.wait_i", "P1.pairs+publish", "P2", "P3.wait", "P3.lists", "exit",
+             "-", "-", "-", "xchg.wait_total", "xchg.count", "-", "-"]
+    print("  ns/step by phase (CTA 0, v2): " + "  ".join(f"{nm} {v / max(ps, 1):.0f}" for nm, v in zip(names, prof) if v))
+elif any(prof):
     names = ["P1a", "P1b", "bar1", "P2", "bar2", "P3", "exit", "-", "b.stage", "b.sync", "b.pairs", "b.foldsync", "-", "-", "-", "-"]
     print("  ns/step by phase (CTA 0): " + "  ".join(f"{nm} {v / max(ps, 1):.0f}" for nm, v in zip(names, prof) if v))
     for nm, base in (("CTA 0", 16), ("CTA G/2", 80)):
