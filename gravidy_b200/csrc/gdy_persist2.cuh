@@ -33,6 +33,7 @@
 namespace gdy {
 
 constexpr int P2_OWN = 64;       // owned active particles a CTA corrects per round of P2
+constexpr int P2_STASH = 16;
 constexpr int P2_NPROF = 16;
 
 struct Persist2Args
@@ -84,6 +85,11 @@ struct P2Fixed
     uint32_t wcnt[PS_W];
     uint16_t own[PS_NACT_CAP];    // k of the active particles this CTA owns
     uint32_t nown;
+    // what the owner already has in hand in phase A, kept for the corrector (first P2_STASH owned particles)
+    double odt[P2_STASH];         // the particle's current step
+    Pred6 opred[P2_STASH];        // its prediction at ITIME
+    double wmin[PS_W];            // phase B: per-warp minimum of t+dt and how many attain it
+    unsigned long long prof[P2_NPROF];   // phase timers of CTA 0 (flushed to global memory once, at exit)
 };
 
 // the CTA whose slice [len*c/G, len*(c+1)/G) holds x  (x < len)
@@ -206,7 +212,9 @@ k_persist2(const Persist2Args a)
     const bool prof = a.prof != nullptr && cta == 0 && tid == 0;
     unsigned long long tp = prof ? gtimer() : 0ull;
 #define GDY_PROF2(slot) \
-    do { if (prof) { const unsigned long long tn_ = gtimer(); a.prof[slot] += tn_ - tp; tp = tn_; } } while (0)
+    do { if (prof) { const unsigned long long tn_ = gtimer(); sm.prof[slot] += tn_ - tp; tp = tn_; } } while (0)
+    if (prof)
+        for (int q = 0; q < P2_NPROF; ++q) sm.prof[q] = 0ull;
 
     // ---- load the slices ------------------------------------------------------------------------------------------
     for (uint32_t q = tid; q < Lf; q += PS_T)
@@ -242,8 +250,10 @@ k_persist2(const Persist2Args a)
             const uint32_t i = sm.ilist[k];
             if (owner(i) == cta)
             {
-                sm.own[atomicAdd(&sm.nown, 1u)] = (uint16_t)k;
+                const uint32_t pos = atomicAdd(&sm.nown, 1u);
+                sm.own[pos] = (uint16_t)k;
                 const Pred6 p = predict_raw(get_raw(i), itime);
+                if (pos < (uint32_t)P2_STASH) { sm.opred[pos] = p; sm.odt[pos] = ldc(s.dt + i); }
                 uint4 *o = a.ipub + (size_t)k * 6;
                 ll_store(o + 0, p.x, tag); ll_store(o + 1, p.y, tag); ll_store(o + 2, p.z, tag);
                 ll_store(o + 3, p.vx, tag); ll_store(o + 4, p.vy, tag); ll_store(o + 5, p.vz, tag);
@@ -269,20 +279,31 @@ k_persist2(const Persist2Args a)
                 const double v = tn[q];
                 if (!due_at(itime, v)) m = fmin(m, v);
             }
-            const double mm = block_min_ps(m, sm);
+#pragma unroll
+            for (int off = 16; off; off >>= 1) m = fmin(m, __shfl_xor_sync(0xffffffffu, m, off));
+            // how many of this warp's sub-slice attain the WARP's minimum; one barrier, then every thread folds the 16
+            // (minimum, count) pairs for itself
             uint32_t c = 0;
-            if (mm < INF)
+            if (m < INF)
                 for (uint32_t q0 = b0; q0 < b1; q0 += 32)
                 {
                     const uint32_t q = q0 + lane;
-                    const bool on = q < b1 && tn[q] == mm && !due_at(itime, tn[q]);
+                    const bool on = q < b1 && tn[q] == m;   // m is not due now, so neither is an entry equal to it
                     c += __popc(__ballot_sync(0xffffffffu, on));
                 }
-            if (lane == 0) sm.wcnt[w] = c;
+            if (lane == 0) { sm.wmin[w] = m; sm.wcnt[w] = c; }
             __syncthreads();
-            uint32_t woff = 0, tot = 0;
+            double mm = sm.wmin[0];
 #pragma unroll
-            for (int ww = 0; ww < PS_W; ++ww) { if (ww < w) woff += sm.wcnt[ww]; tot += sm.wcnt[ww]; }
+            for (int ww = 1; ww < PS_W; ++ww) mm = fmin(mm, sm.wmin[ww]);
+            uint32_t woff = 0, tot = 0;
+            if (mm < INF)
+            {
+#pragma unroll
+                for (int ww = 0; ww < PS_W; ++ww)
+                    if (sm.wmin[ww] == mm) { if (ww < w) woff += sm.wcnt[ww]; tot += sm.wcnt[ww]; }
+            }
+            if (!(m == mm)) c = 0;   // this warp's sub-slice does not attain the slice minimum
             // clist[par] is rewritten two steps later; its readers (P3 of this step, every CTA) are through by then:
             // a CTA reaches B of step+2 only after P3 of step+1, which needs every CTA's partials of step+1, which
             // they publish after their P3 of this step.
@@ -293,7 +314,7 @@ k_persist2(const Persist2Args a)
                 for (uint32_t q0 = b0; q0 < b1; q0 += 32)
                 {
                     const uint32_t q = q0 + lane;
-                    const bool on = q < b1 && tn[q] == mm && !due_at(itime, tn[q]);
+                    const bool on = q < b1 && tn[q] == mm;
                     const uint32_t bal = __ballot_sync(0xffffffffu, on);
                     const uint32_t at = pos + __popc(bal & ((1u << lane) - 1u));
                     if (on && at < a.lcap) ll2_store(list + at, s0 + q, tag);
@@ -396,7 +417,8 @@ k_persist2(const Persist2Args a)
                     const uint32_t i = sm.ilist[k];
                     Raw13 ri{};
                     double dt1 = 0.0;
-                    if (lane == 0) { ri = get_raw(i); dt1 = ldc(s.dt + i); }   // in flight during the exchange
+                    const bool stashed = o0 + o < (uint32_t)P2_STASH;
+                    if (lane == 0) { ri = get_raw(i); dt1 = stashed ? sm.odt[o0 + o] : ldc(s.dt + i); }   // in flight during the exchange
                     double f[6];
 #pragma unroll
                     for (int c = 0; c < 6; ++c) f[c] = sm.fs[o * 6 + c];
@@ -461,7 +483,7 @@ k_persist2(const Persist2Args a)
                         s.old[3][i] = ri.f3; s.old[4][i] = ri.f4; s.old[5][i] = ri.f5;
 #pragma unroll
                         for (int c = 0; c < 6; ++c) s.f[c][i] = f[c];
-                        q.p = predict_raw(ri, itime);
+                        q.p = stashed ? sm.opred[o0 + o] : predict_raw(ri, itime);
                         store_pred(s, i, q.p);   // h_p of the active particles stays what the reference leaves there
                         const CorrOut co = correct_core(s, i, itime, a.eta, q);
                         const uint32_t qq = i - fj0;
@@ -613,6 +635,8 @@ k_persist2(const Persist2Args a)
         h->seq = c.seq;
     }
     GDY_PROF2(8);
+    if (prof)
+        for (int q = 0; q < P2_NPROF; ++q) if (q != 12 && q != 13) a.prof[q] += sm.prof[q];   // 12, 13: the owners' exchange waits (atomics)
 #undef GDY_PROF2
 }
 

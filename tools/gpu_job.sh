@@ -32,8 +32,9 @@ for st in "$@"; do
       timeout 900 python bench.py --impl reference > $O/${TAG}_bench_reference.json 2> $O/${TAG}_bench_reference.err
       echo "[$st] rc=$? $(tail -c 300 $O/${TAG}_bench_reference.json)";;
     lat)
-      GDY_PERSIST_PROF=1 timeout 600 python tools/step_latency.py --n $a1 --spectrum ${a2:-equal} ${a3:+--steps $a3} > $O/${TAG}_lat_n$a1.txt 2>&1
-      echo "[$st] rc=$?"; head -30 $O/${TAG}_lat_n$a1.txt;;
+      timeout 600 python tools/step_latency.py --n $a1 --spectrum ${a2:-equal} ${a3:+--steps $a3} > $O/${TAG}_lat_n$a1.txt 2>&1
+      echo "[$st] rc=$?"; head -30 $O/${TAG}_lat_n$a1.txt
+      GDY_PERSIST_PROF=1 timeout 600 python tools/step_latency.py --n $a1 --spectrum ${a2:-equal} ${a3:+--steps $a3} 2>&1 | grep -E "ns/step|median" | head -4;;
     integ)
       g=${a3:-1}
       if [ "$g" = 1 ]; then env ${a4:-X=1} timeout 900 python tools/integrate.py --particles $a1 --tend $a2 --rank-prof $O/${TAG}_integ_n${a1}_${g}gpu > $O/${TAG}_integ_n${a1}_${g}gpu.json 2> $O/${TAG}_integ_n${a1}_${g}gpu.err
