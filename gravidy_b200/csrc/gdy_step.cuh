@@ -97,7 +97,15 @@ __global__ void k_init_pb(State s, uint32_t n, uint32_t npad)
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= npad) return;
     double *q = s.pb + pbidx(i, 0);
-    if (i < n) q[6 * JB] = s.m[i];
+    if (i < n)
+    {
+        // The reference keeps every mass as a float: the reader narrows it (NbodySystem.cpp:174) and so does Predictor.m
+        // (common.hpp:216), which is what the force loop reads.  A caller of the C ABI that hands over a mass that is
+        // not float-representable gets the same narrowing here, once, for every array that holds the mass.
+        const double mf = (double)(float)s.m[i];
+        s.m[i] = mf;
+        q[6 * JB] = mf;
+    }
     else
     {
         q[0] = PAD_POS; q[JB] = PAD_POS; q[2 * JB] = PAD_POS;

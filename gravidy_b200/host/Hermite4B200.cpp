@@ -186,8 +186,9 @@ struct CkptHeader
     double e2;
     float eta, reserved2;
     double ITIME, ATIME, e_ini, e_tmp;
+    double update_end;   // seconds spent in force evaluations so far: the log's GFLOPS column is interactions / this
 };
-const char CKPT_MAGIC[8] = {'G', 'D', 'Y', 'C', 'K', 'P', 'T', '1'};
+const char CKPT_MAGIC[8] = {'G', 'D', 'Y', 'C', 'K', 'P', 'T', '2'};
 }  // namespace
 
 void Hermite4B200::write_checkpoint(const LoopState &ls)
@@ -200,6 +201,7 @@ void Hermite4B200::write_checkpoint(const LoopState &ls)
     h.iterations = ns->iterations; h.nsteps = ls.nsteps; h.interactions = ls.interactions;
     h.e2 = ns->e2; h.eta = ns->eta;
     h.ITIME = ls.ITIME; h.ATIME = ls.ATIME; h.e_ini = ns->en.ini; h.e_tmp = ns->en.tmp;
+    h.update_end = ns->gtime.update_end;
     const std::string name = ns->output_filename + ".ckpt", tmp = name + ".tmp";
     {
         std::ofstream out(tmp.c_str(), std::ios::out | std::ios::binary | std::ios::trunc);
@@ -263,6 +265,7 @@ void Hermite4B200::read_checkpoint(LoopState &ls)
     ls.snap_number = h.snap_number; ls.interactions = h.interactions;
     ns->iterations = h.iterations;
     ns->en.ini = h.e_ini; ns->en.tmp = h.e_tmp;
+    ns->gtime.update_end = h.update_end;   // GFLOPS of the restarted run's log lines stay interactions / force time
     each_shard([&](int g) {
         check(gdy_upload_particles(shards[g], &ns->h_r[0].x, &ns->h_v[0].x), g, "gdy_upload_particles");
         check(gdy_upload_forces(shards[g], &ns->h_f[0].a[0]), g, "gdy_upload_forces");

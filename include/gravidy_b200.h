@@ -78,6 +78,11 @@ const char *gdy_last_error(const gdy_ctx *ctx); /* ctx may be NULL: last create(
 /* ---- state transfer ---------------------------------------------------------------------------
  * Replaces the per-step cudaMemcpy of the whole particle set (reference: Hermite4GPU.cu:226-265,
  * 338-346): state goes up once and comes down only at output points. */
+/* r4 = n x {x, y, z, m}, v4 = n x {vx, vy, vz, unused}.  The mass is narrowed to float and widened again on the device,
+ * (double)(float)m, because that is what the reference computes with (its reader and Predictor.m are float:
+ * src/include/NbodySystem.cpp:174, src/include/common.hpp:216); masses that come from the reference's own reader are
+ * unchanged by it.  Collective on sharded contexts with a communicator (every rank passes the same arrays, copies only
+ * its 1/world of them over PCIe and the chunks are all-gathered over NVLink). */
 int gdy_upload_particles(gdy_ctx *ctx, const double *r4, const double *v4);
 int gdy_upload_times(gdy_ctx *ctx, const double *t, const double *dt); /* after host init_dt */
 int gdy_upload_forces(gdy_ctx *ctx, const double *f6);                 /* tests / resume     */

@@ -109,7 +109,7 @@ def test_lagrange_radii_and_resume(binary, tmp_path):
 CKPT_HEADER = np.dtype([("magic", "S8"), ("n", "<u4"), ("snap_number", "<u4"), ("output_factor", "<u4"),
                         ("iterations", "<u4"), ("nsteps", "<u4"), ("reserved", "<u4"), ("interactions", "<i8"),
                         ("e2", "<f8"), ("eta", "<f4"), ("reserved2", "<f4"), ("ITIME", "<f8"), ("ATIME", "<f8"),
-                        ("e_ini", "<f8"), ("e_tmp", "<f8")])
+                        ("e_ini", "<f8"), ("e_tmp", "<f8"), ("update_end", "<f8")])
 
 
 def read_ckpt(path):
@@ -137,14 +137,19 @@ def test_checkpoint_restart_continues_the_schedule_bit_for_bit(binary, tmp_path,
     p = subprocess.run(common + ["-t", "0.25"], cwd=b, capture_output=True, text=True, timeout=300)
     assert p.returncode == 0, p.stderr
     half = read_ckpt(b / "run.out.ckpt")
-    assert half[0]["magic"] == b"GDYCKPT1" and half[0]["ITIME"] == 0.25 and half[0]["n"] == 64
+    assert half[0]["magic"] == b"GDYCKPT2" and half[0]["ITIME"] == 0.25 and half[0]["n"] == 64
     shutil.copy(b / "run.out.ckpt", b / "half.ckpt")
     p = subprocess.run(common + ["-t", "0.5", "--restart", "./half.ckpt"], cwd=b, capture_output=True, text=True,
                        timeout=300)
     assert p.returncode == 0, p.stderr
     ha, hb = read_ckpt(a / "run.out.ckpt"), read_ckpt(b / "run.out.ckpt")
     for name in CKPT_HEADER.names:
-        assert ha[0][name] == hb[0][name], name
+        if name != "update_end":   # wall-clock seconds spent in force evaluations
+            assert ha[0][name] == hb[0][name], name
+    # the force time carries over the restart, so the GFLOPS column stays interactions / force time (never inf)
+    assert hb[0]["update_end"] > half[0]["update_end"] > 0.0
+    for ln in open(b / "run.out.log").read().splitlines()[1:]:
+        assert np.isfinite(float(ln.split()[-1])), ln
     assert ha[0]["ITIME"] == 0.5 and ha[0]["iterations"] > half[0]["iterations"]
     for x, y in zip(ha[1:], hb[1:]):
         assert np.array_equal(x, y)

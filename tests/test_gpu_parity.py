@@ -244,6 +244,17 @@ def test_run_n1024_to_t1_vs_reference_fixture(H, golden_dir):
     assert 0.1 < err_gpu / err_ref < 10.0, (err_gpu, err_ref)   # same decade
 
 
+def test_masses_are_narrowed_to_float_like_the_reference(H):
+    """The reference computes with float masses (NbodySystem.cpp:174, common.hpp:216): a C-ABI caller that passes a mass
+    that is not float-representable gets (double)(float)m, not a different schedule."""
+    m, r, v = plummer(300, seed=5, mass_spectrum="salpeter")
+    a, b = H(m * (1.0 + 3e-9), r, v), H((m * (1.0 + 3e-9)).astype(np.float32).astype(np.float64), r, v)
+    a.init_acc_jrk(); b.init_acc_jrk()
+    assert np.array_equal(a.download_forces(), b.download_forces())
+    assert np.array_equal(a.get_state("r4")["r4"][:, 3], b.get_state("r4")["r4"][:, 3])
+    assert a.get_energy() == b.get_energy()
+
+
 def test_energy_vs_oracle(H, O):
     n = 5000
     m, r, v = plummer(n, seed=21, mass_spectrum="salpeter")
