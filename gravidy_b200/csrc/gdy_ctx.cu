@@ -108,21 +108,14 @@ struct gdy_ctx
     uint64_t launches = 0;
     double force_ms_acc = 0.0;
 
-    // persistent small-step kernel (gdy_persist.cuh)
+    // persistent small-step kernel (gdy_persist2.cuh)
     uint32_t ps_nact_max = 0;        // 0 = off
-    uint32_t ps_grid = 0, ps_slice = 0, ps_gpad = 0;
-    uint4 *ps_part = nullptr;
-    double *ps_cta_min = nullptr, *ps_act_next = nullptr;
-    uint32_t *ps_cta_cnt = nullptr, *ps_cta_list = nullptr, *ps_flags = nullptr, *ps_exit_cnt = nullptr;
-    unsigned long long *ps_prof = nullptr;
+    uint32_t ps_grid = 0, ps_gpad = 0;
     PersistCtl *ps_ctl = nullptr, *ps_ctl_host = nullptr;
     TraceRec *ps_trace_host = nullptr;
-    uint32_t ps_epoch = 0;
-    uint32_t ps_seq = 0, ps_xseq = 0, ps_xcount = 0;
-    uint32_t ps_repl_nact = 0;   // sharded runs: blocks this small are evaluated replicated (gdy_persist.cuh)
+    uint32_t ps_seq = 0, ps_xseq = 0;
     bool ps_last = false;            // the last block step was done by the persistent kernel
-    // second design of the persistent kernel (gdy_persist2.cuh): flagged-slot buffers and the shared-memory carve-up
-    int ps_version = 2;              // GDY_PERSIST_V=1 selects the first design (grid barriers)
+    // its flagged-slot buffers and the shared-memory carve-up
     bool p2_ready = false;
     uint4 *p2_ipub = nullptr, *p2_part = nullptr, *p2_anext = nullptr, *p2_cmin = nullptr;
     uint2 *p2_ccnt = nullptr, *p2_clist = nullptr, *p2_ecnt = nullptr;
@@ -296,38 +289,20 @@ int alloc_all(gdy_ctx *c)
     k_init_pb<<<cdiv(c->npad, 256), 256, 0, c->st>>>(s, c->n, c->npad);
     LAUNCHED(c);
     CU(force_variants_prepare());
-    // persistent small-step kernel: one CTA per SM, co-resident (cooperative launch)
+    // persistent small-step kernel: one CTA per SM, co-resident (cooperative launch); its buffers and shared-memory
+    // carve-up follow once the shard range is known (persist2_prepare)
     {
-        int coop = 0, per_sm = 0;
+        int coop = 0;
         CU(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, c->device));
-        CU(cudaFuncSetAttribute((const void *)k_persist_steps<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PersistSmem)));
-        CU(cudaFuncSetAttribute((const void *)k_persist_steps<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PersistSmem)));
-        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, (const void *)k_persist_steps<false>, PS_T, sizeof(PersistSmem)));
         c->ps_grid = (uint32_t)c->num_sms;
         // GDY_PS_GRID: fewer CTAs than SMs, so that two logical ranks can run their persistent kernels side by side
         // on ONE device (tests of the peer-memory exchange on a single-GPU box)
         if (const char *e = getenv("GDY_PS_GRID")) { const int g = atoi(e); if (g >= 1 && g <= c->num_sms) c->ps_grid = (uint32_t)g; }
         if (c->ps_grid > (uint32_t)PS_GMAX) c->ps_grid = PS_GMAX;
-        if (const char *e = getenv("GDY_PERSIST_V")) c->ps_version = atoi(e) == 1 ? 1 : 2;
         if (const char *e = getenv("GDY_XMID")) c->use_xmid = atoi(e) != 0;
         if (const char *e = getenv("GDY_SHARDED_UPLOAD")) c->sharded_upload = atoi(e) != 0;
         if (const char *e = getenv("GDY_SPIN_TIMEOUT_MS")) { const long ms = atol(e); if (ms > 0) c->spin_timeout_ns = (unsigned long long)ms * 1000000ull; }
-        c->ps_slice = round_up(cdiv(c->n, c->ps_grid), 2);   // even: the list heads are read as uint2
         c->ps_gpad = round_up(c->ps_grid, 32);
-        CU(cudaMalloc(&c->ps_part, (size_t)PS_NACT_CAP * 6 * c->ps_gpad * sizeof(uint4)));
-        CU(cudaMemsetAsync(c->ps_part, 0, (size_t)PS_NACT_CAP * 6 * c->ps_gpad * sizeof(uint4), c->st));
-        CU(cudaMalloc(&c->ps_cta_min, 2 * c->ps_grid * sizeof(double)));
-        CU(cudaMalloc(&c->ps_act_next, PS_NACT_CAP * sizeof(double)));
-        CU(cudaMalloc(&c->ps_cta_cnt, 2 * c->ps_grid * sizeof(uint32_t)));
-        CU(cudaMalloc(&c->ps_cta_list, (size_t)2 * c->ps_grid * c->ps_slice * sizeof(uint32_t)));
-        CU(cudaMalloc(&c->ps_exit_cnt, c->ps_grid * sizeof(uint32_t)));
-        CU(cudaMalloc(&c->ps_flags, c->ps_grid * sizeof(uint32_t)));
-        CU(cudaMemsetAsync(c->ps_flags, 0, c->ps_grid * sizeof(uint32_t), c->st));
-        if (getenv("GDY_PERSIST_PROF"))
-        {
-            CU(cudaMalloc(&c->ps_prof, PS_NPROF * sizeof(unsigned long long)));
-            CU(cudaMemsetAsync(c->ps_prof, 0, PS_NPROF * sizeof(unsigned long long), c->st));
-        }
         CU(cudaMalloc(&c->ps_ctl, sizeof(PersistCtl)));
         CU(cudaHostAlloc(&c->ps_ctl_host, sizeof(PersistCtl), cudaHostAllocDefault));
         CU(cudaHostAlloc(&c->ps_trace_host, PS_STEPS_MAX * sizeof(TraceRec), cudaHostAllocDefault));
@@ -335,7 +310,7 @@ int alloc_all(gdy_ctx *c)
         uint32_t def = PS_DEFAULT_NACT;
         if (const char *e = getenv("GDY_PERSIST_NACT")) def = (uint32_t)atoi(e);
         if (def > (uint32_t)PS_NACT_CAP) def = PS_NACT_CAP;
-        if (!coop || per_sm < 1) def = 0;
+        if (!coop) def = 0;
         // sharded contexts join the persistent path once their peers are attached (gdy_peer_attach)
         c->ps_nact_max = c->world == 1 ? def : 0;
     }
@@ -432,9 +407,7 @@ extern "C" int gdy_destroy(gdy_ctx *c)
     cudaFree(c->pool); cudaFree(c->d_move); cudaFree(c->d_ilist); cudaFree(c->d_block_cnt);
     cudaFree(c->d_block_min); cudaFree(c->d_sched); cudaFree(c->d_atime); cudaFree(c->d_energy);
     cudaFree(c->d_stage); cudaFree(c->d_counter);
-    cudaFree(c->ps_part); cudaFree(c->ps_cta_min); cudaFree(c->ps_act_next); cudaFree(c->ps_cta_cnt);
-    cudaFree(c->ps_cta_list); cudaFree(c->ps_flags); cudaFree(c->ps_exit_cnt); cudaFree(c->ps_ctl);
-    cudaFree(c->ps_prof);
+    cudaFree(c->ps_ctl);
     cudaFree(c->p2_ipub); cudaFree(c->p2_part); cudaFree(c->p2_anext); cudaFree(c->p2_cmin); cudaFree(c->p2_ccnt);
     cudaFree(c->p2_clist); cudaFree(c->p2_ecnt); cudaFree(c->p2_abort); cudaFree(c->p2_prof);
     for (int r = 0; r < PS_MAX_WORLD; ++r)
@@ -614,7 +587,7 @@ int pick_variant(const gdy_ctx *c, uint32_t nact)
     if (nact <= 160 || (uint64_t)nact * nj <= 12000000ull) return FV_LANE_I1x4;
     // the smallest i-tile of the TMA-ring family at every size: with ~24 waves of small CTAs (plan_force) the
     // block scheduler balances the SMs dynamically, and a CTA's prologue hides behind its neighbours' FP64 work
-    // (profiles/r01_sweep_split_v11.md: 517 vs 508 Gpairs/s for warp_i256 at full-active N = 256k)
+    // (profiles/archive/r01_sweep_split_v11.md: 517 vs 508 Gpairs/s for warp_i256 at full-active N = 256k)
     return FV_WARP_I64;
 }
 
@@ -646,7 +619,7 @@ ForcePlan plan_force(const gdy_ctx *c, uint32_t nact)
     if (c->tune_jsplit > 0) split = (uint32_t)c->tune_jsplit;
     else if (units > 1 && v.kind == 0)
     {
-        // Warp kernels: many small CTAs.  Measured (tools/sweep_split.py, profiles/r01_sweep_split_v11.md): the rate
+        // Warp kernels: many small CTAs.  Measured (tools/sweep_split.py, profiles/archive/r01_sweep_split_v11.md): the rate
         // keeps rising until ~20-28 waves of CTAs and down to ~16 j-blocks per CTA — the one-wave plans of the old
         // wave model lost 2-8 % at awkward sizes (an SM that is a little slower, or has 3 CTAs instead of 4,
         // decides the time), while per-CTA fixed costs overlap with the other resident CTAs' FP64 work.
@@ -1138,7 +1111,7 @@ int persist2_prepare(gdy_ctx *c)
     return 0;
 }
 
-int run_persist2(gdy_ctx *c, double itime, uint32_t nact, double t_stop, uint32_t budget, bool timed, float *ms_out)
+int run_persist(gdy_ctx *c, double itime, uint32_t nact, double t_stop, uint32_t budget, bool timed, float *ms_out)
 {
     Persist2Args a{};
     a.s = c->s; a.n = c->n;
@@ -1186,51 +1159,6 @@ int run_persist2(gdy_ctx *c, double itime, uint32_t nact, double t_stop, uint32_
     // tags: one per step, one for the exit exchange, and one more so that the next launch's first step has the other
     // exchange-slot parity than this launch's last
     c->ps_xseq += c->ps_ctl_host->steps + 2;
-    c->ps_steps_total += c->ps_ctl_host->steps;
-    if (ms_out)
-    {
-        *ms_out = 0.f;
-        if (timed) CU(cudaEventElapsedTime(ms_out, c->ev0, c->ev1));
-    }
-    return 0;
-}
-
-int run_persist(gdy_ctx *c, double itime, uint32_t nact, double t_stop, uint32_t budget, bool timed, float *ms_out)
-{
-    if (c->ps_version == 2 && c->p2_ready) return run_persist2(c, itime, nact, t_stop, budget, timed, ms_out);
-    PersistArgs a{};
-    a.s = c->s; a.n = c->n;
-    a.jb = c->blk_begin * JB;
-    a.je = c->blk_end * JB < c->n ? c->blk_end * JB : c->n;
-    if (a.je < a.jb) a.je = a.jb;
-    a.e2 = c->e2; a.eta = (double)c->eta; a.t_stop = t_stop;
-    a.entry_itime = itime; a.entry_nact = nact;
-    a.max_steps = budget < PS_STEPS_MAX ? budget : PS_STEPS_MAX;
-    a.nact_max = c->ps_nact_max;
-    a.slice = c->ps_slice; a.seq = ++c->ps_seq;
-    a.part = c->ps_part; a.gpad = c->ps_gpad; a.cta_min = c->ps_cta_min; a.cta_cnt = c->ps_cta_cnt;
-    a.cta_list = c->ps_cta_list; a.act_next = c->ps_act_next; a.flags = c->ps_flags; a.exit_cnt = c->ps_exit_cnt;
-    a.prof = c->ps_prof;
-    a.ctl_dev = c->ps_ctl; a.ctl_host = c->ps_ctl_host; a.trace = c->ps_trace_host;
-    a.epoch0 = c->ps_epoch;
-    a.rank = c->rank; a.world = c->peers_ok ? c->world : 1;
-    a.xseq0 = c->ps_xseq;
-    a.xcount0 = c->ps_xcount;
-    a.repl_nact = a.world > 1 ? c->ps_repl_nact : 0;
-    for (int r = 0; r < PS_MAX_WORLD; ++r) a.xslot[r] = c->xslot[r];
-    if (timed) CU(cudaEventRecord(c->ev0, c->st));
-    void *args[] = {&a};
-    const void *fn = c->mask_self ? (const void *)k_persist_steps<true> : (const void *)k_persist_steps<false>;
-    CU(cudaLaunchCooperativeKernel(fn, dim3(c->ps_grid), dim3(PS_T), args, sizeof(PersistSmem), c->st));
-    ++c->launches; ++c->ps_launches;
-    if (timed) CU(cudaEventRecord(c->ev1, c->st));
-    CU(cudaStreamSynchronize(c->st));
-    if (c->ps_ctl_host->seq != a.seq) return fail(c, GDY_ERR_STATE, "persistent kernel left no result (seq %u != %u)", c->ps_ctl_host->seq, a.seq);
-    c->ps_epoch = c->ps_ctl_host->epoch_end;
-    c->ps_xseq += c->ps_ctl_host->steps;
-    if (a.world > 1)   // exchanges this launch did: every step whose block was not replicated (same count on every rank)
-        for (uint32_t k = 0; k < c->ps_ctl_host->steps; ++k)
-            if (c->ps_trace_host[k].nact > a.repl_nact) ++c->ps_xcount;
     c->ps_steps_total += c->ps_ctl_host->steps;
     if (ms_out)
     {
@@ -1324,27 +1252,17 @@ extern "C" int gdy_peer_attach(gdy_ctx *c, const uint8_t *handles)
     if (const char *e = getenv("GDY_PERSIST_NACT")) def = (uint32_t)atoi(e);
     if (def > (uint32_t)PS_NACT_CAP) def = PS_NACT_CAP;
     c->ps_nact_max = def;
-    // tiny blocks: one pass over all N on every rank beats a pass over N/world plus the exchange
-    // (measured per block step, N = 256k: profiles/r01_repl_small_steps_v10.md)
-    c->ps_repl_nact = PS_DEFAULT_REPL_NACT;
-    if (const char *e = getenv("GDY_REPL_NACT")) c->ps_repl_nact = (uint32_t)atoi(e);
     return GDY_OK;
 }
 
 // ns spent per phase of the persistent kernel by CTA 0 (only with GDY_PERSIST_PROF=1 in the environment)
-extern "C" int gdy_persist_profile(gdy_ctx *c, uint64_t *ns_out /* [PS_NPROF = 144] */)
+extern "C" int gdy_persist_profile(gdy_ctx *c, uint64_t *ns_out /* [144]: the first P2_NPROF = 16 are used */)
 {
     if (!c || !ns_out) return GDY_ERR_INVALID;
     BIND(c);
-    memset(ns_out, 0, PS_NPROF * sizeof(uint64_t));
-    if (c->ps_version == 2 && c->p2_prof)   // second design: P2_NPROF slots (tools/step_latency.py names them)
-    {
-        CU(cudaMemcpyAsync(ns_out, c->p2_prof, P2_NPROF * sizeof(uint64_t), cudaMemcpyDeviceToHost, c->st));
-        CU(cudaStreamSynchronize(c->st));
-        return GDY_OK;
-    }
-    if (!c->ps_prof) return GDY_OK;
-    CU(cudaMemcpyAsync(ns_out, c->ps_prof, PS_NPROF * sizeof(uint64_t), cudaMemcpyDeviceToHost, c->st));
+    memset(ns_out, 0, 144 * sizeof(uint64_t));
+    if (!c->p2_prof) return GDY_OK;
+    CU(cudaMemcpyAsync(ns_out, c->p2_prof, P2_NPROF * sizeof(uint64_t), cudaMemcpyDeviceToHost, c->st));
     CU(cudaStreamSynchronize(c->st));
     return GDY_OK;
 }
@@ -1386,8 +1304,8 @@ extern "C" int gdy_run(gdy_ctx *c, double atime, double itime0, double t_stop, u
     {
         if (max_steps && it >= max_steps) break;
         const uint32_t nact = c->pin->sched.nact;
-        if (c->ps_nact_max && c->ps_version == 2 && !c->p2_ready && c->p2_smem != 1 && (r = persist2_prepare(c))) return r;
-        if (c->ps_nact_max && nact && nact <= c->ps_nact_max && (c->ps_version == 1 || c->p2_ready))
+        if (c->ps_nact_max && !c->p2_ready && c->p2_smem != 1 && (r = persist2_prepare(c))) return r;
+        if (c->ps_nact_max && nact && nact <= c->ps_nact_max && c->p2_ready)
         {
             // small active set: stay on the device until a big block (or t_stop / the step budget) comes up
             const uint64_t left = max_steps ? max_steps - it : PS_STEPS_MAX;

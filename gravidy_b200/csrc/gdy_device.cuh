@@ -160,7 +160,7 @@ __device__ __forceinline__ void pair(Acc6 &s, double xi, double yi, double zi, d
 // The same pair in two halves: pair_head leaves (d, dv, m/r^3, c) in registers, pair_tail does the nine
 // three-source DFMAs.  Written apart so that the DFMAs that share m/r^3 (six) and c (three) can sit next to each
 // other in the SASS: an operand the previous DFMA of the warp flagged `.reuse` is not read from the register file,
-// which is what limits a three-source DFMA to 3/4 rate (tools/fp64_reuse.cu, profiles/r01_fp64_reuse_v9.md).
+// which is what limits a three-source DFMA to 3/4 rate (tools/fp64_reuse.cu, profiles/archive/r01_fp64_reuse_v9.md).
 struct PairMid { double dx, dy, dz, dvx, dvy, dvz, mr3, c; };
 
 template <bool MASK_SELF>

@@ -27,7 +27,7 @@
 // their tails (pair_head / pair_tail; putting a tail into ONE asm statement changes nothing: ptxas reorders it);
 // 3 = software-pipelined: the six-DFMA tails of the previous trip's pairs, which all share m/r^3, issue while this
 // trip's LDS.128 are in flight, then this trip's heads.  tools/force_lab.sh builds them side by side;
-// measured (profiles/r01_force_lab_v9.md): form 3, unroll 1, 512 resident threads is the fastest, 508 Gpairs/s.
+// measured (profiles/archive/r01_force_lab_v9.md): form 3, unroll 1, 512 resident threads is the fastest, 508 Gpairs/s.
 #ifndef GDY_FORCE_FORM
 #define GDY_FORCE_FORM 3
 #endif

@@ -88,7 +88,9 @@ struct P2Fixed
     // what the owner already has in hand in phase A, kept for the corrector (first P2_STASH owned particles)
     double odt[P2_STASH];         // the particle's current step
     Pred6 opred[P2_STASH];        // its prediction at ITIME
-    double wmin[PS_W];            // phase B: per-warp minimum of t+dt and how many attain it
+    double wmin[PS_W];            // phase B: per-warp minimum of t+dt and how many attain it; P3: per-warp minimum
+    uint32_t wa[PS_W], wb[PS_W];  // P3: per-warp counts of the two next-list sources
+    uint32_t big;                 // P3: some slice has more than two candidates
     unsigned long long prof[P2_NPROF];   // phase timers of CTA 0 (flushed to global memory once, at exit)
 };
 
@@ -202,6 +204,38 @@ k_persist2(const Persist2Args a)
     double itime = a.entry_itime;
     uint32_t nact = a.entry_nact;
     uint32_t steps = 0;
+    uint32_t tag = 0;
+    // Lane 0 of the calling warp corrects active particle k (position `opos` of this CTA's owned list) with the summed
+    // force f: save_old_acc_jrk and the force store of update_acc_jrk fused, Hermite corrector, new timestep level; the
+    // resident copy is patched and the particle's new t+dt published.
+    auto correct_owned = [&](uint32_t k, uint32_t opos, const double *f) {
+        if (lane != 0) return;
+        const uint32_t i = sm.ilist[k];
+        const Raw13 ri = get_raw(i);
+        const bool stashed = opos < (uint32_t)P2_STASH;
+        CorrIn q;
+        q.dt1 = stashed ? sm.odt[opos] : ldc(s.dt + i);
+        q.oa[0] = ri.f0; q.oa[1] = ri.f1; q.oa[2] = ri.f2; q.oj[0] = ri.f3; q.oj[1] = ri.f4; q.oj[2] = ri.f5;
+#pragma unroll
+        for (int c = 0; c < 3; ++c) { q.fa[c] = f[c]; q.fj[c] = f[3 + c]; }
+        s.old[0][i] = ri.f0; s.old[1][i] = ri.f1; s.old[2][i] = ri.f2;
+        s.old[3][i] = ri.f3; s.old[4][i] = ri.f4; s.old[5][i] = ri.f5;
+#pragma unroll
+        for (int c = 0; c < 6; ++c) s.f[c][i] = f[c];
+        q.p = stashed ? sm.opred[opos] : predict_raw(ri, itime);
+        store_pred(s, i, q.p);   // h_p of the active particles stays what the reference leaves there
+        const CorrOut co = correct_core(s, i, itime, a.eta, q);
+        const uint32_t qq = i - fj0;
+        if (qq < R)   // patch the resident copy
+        {
+            rs[qq] = itime; rs[RC + qq] = co.x; rs[2 * RC + qq] = co.y; rs[3 * RC + qq] = co.z;
+            rs[4 * RC + qq] = co.vx; rs[5 * RC + qq] = co.vy; rs[6 * RC + qq] = co.vz;
+#pragma unroll
+            for (int c = 0; c < 6; ++c) rs[(7 + c) * RC + qq] = f[c];
+        }
+        // anext[k] is rewritten a step later, behind every CTA's P3 of this step (see A)
+        ll_store(a.anext + k, add(itime, co.ndt), tag);
+    };
     uint64_t sum_nact = 0;
     double last_itime = itime;
     uint32_t last_nact = 0;
@@ -238,7 +272,7 @@ k_persist2(const Persist2Args a)
 
     for (;;)
     {
-        const uint32_t tag = a.tag0 + steps + 1;
+        tag = a.tag0 + steps + 1;
         const uint32_t par = tag & 1u;
 
         // ---- A: the owners publish the predicted active particles ------------------------------------------------
@@ -410,27 +444,22 @@ k_persist2(const Persist2Args a)
                     if (lane == 0) sm.fs[idx] = v;
                 }
                 if (__syncthreads_or(dead)) { bail = true; break; }
-                // P2b: one warp per particle: exchange over NVLink, then lane 0 corrects
+                // P2b: one warp per particle.  Sharded: the rank's sum goes to EVERY rank's exchange buffer now, the
+                // receive comes in a second pass once ALL owned particles of ALL rounds are on their way — a warp that
+                // waited for particle p before sending particle q could wait for a rank whose own p-owner is behind its
+                // q (the owners and their order differ from rank to rank): a cycle.  Sends never block.
                 for (uint32_t o = w; o < no; o += PS_W)
                 {
                     const uint32_t k = sm.own[o0 + o];
-                    const uint32_t i = sm.ilist[k];
-                    Raw13 ri{};
-                    double dt1 = 0.0;
-                    const bool stashed = o0 + o < (uint32_t)P2_STASH;
-                    if (lane == 0) { ri = get_raw(i); dt1 = stashed ? sm.odt[o0 + o] : ldc(s.dt + i); }   // in flight during the exchange
                     double f[6];
 #pragma unroll
                     for (int c = 0; c < 6; ++c) f[c] = sm.fs[o * 6 + c];
                     if (a.world > 1)
                     {
                         // One-shot all-to-all over NVLink (replaces ncclAllReduce and the reference's host-side sum
-                        // over GPUs, src/include/gpu/Hermite4GPU.cu:512-530): my rank's sum goes as flagged slots
-                        // into buffer [parity][my rank][k] of EVERY rank, then the world's sums are added in rank
-                        // order.  Two parities: a rank is at most one step ahead of the slowest reader (it cannot
-                        // finish step+1 without this rank's sums of step+1).
-                        const unsigned long long tx = a.prof ? gtimer() : 0ull;
-                        double xv[2] = {0.0, 0.0};
+                        // over GPUs, src/include/gpu/Hermite4GPU.cu:512-530): flagged slots into buffer
+                        // [parity][my rank][k] of EVERY rank (mine included).  Two parities: a rank is at most one step
+                        // ahead of the slowest reader (it cannot finish step+1 without this rank's sums of step+1).
 #pragma unroll
                         for (int u = 0; u < 2; ++u)
                         {
@@ -444,62 +473,48 @@ k_persist2(const Persist2Args a)
                                 ll_store_sys(a.xslot[r] + (((size_t)par * PS_MAX_WORLD + a.rank) * PS_NACT_CAP + k) * 6 + c, v, tag);
                             }
                         }
-#pragma unroll
-                        for (int u = 0; u < 2; ++u)
-                        {
-                            const int idx = u * 32 + lane;
-                            if (idx < 6 * a.world)
-                            {
-                                const int r = idx / 6, c = idx % 6;
-                                if (!ll_wait_sys(a.xslot[a.rank] + (((size_t)par * PS_MAX_WORLD + r) * PS_NACT_CAP + k) * 6 + c,
-                                                 tag, xv[u], wd, a, 3)) dead = true;
-                            }
-                        }
-                        __syncwarp();
-#pragma unroll
-                        for (int c = 0; c < 6; ++c)
-                        {
-                            double sum = 0.0;
-                            for (int r = 0; r < a.world; ++r)
-                            {
-                                const int idx = r * 6 + c;
-                                const double v0 = __shfl_sync(0xffffffffu, xv[0], idx & 31);
-                                const double v1 = __shfl_sync(0xffffffffu, xv[1], idx & 31);
-                                sum += idx < 32 ? v0 : v1;
-                            }
-                            f[c] = sum;
-                        }
-                        if (a.prof && lane == 0) { atomicAdd(a.prof + 12, gtimer() - tx); atomicAdd(a.prof + 13, 1ull); }
                     }
-                    if (lane == 0)
-                    {
-                        CorrIn q;
-                        q.dt1 = dt1;
-                        q.oa[0] = ri.f0; q.oa[1] = ri.f1; q.oa[2] = ri.f2; q.oj[0] = ri.f3; q.oj[1] = ri.f4; q.oj[2] = ri.f5;
-#pragma unroll
-                        for (int c = 0; c < 3; ++c) { q.fa[c] = f[c]; q.fj[c] = f[3 + c]; }
-                        // save_old_acc_jrk and the force store of update_acc_jrk, fused
-                        s.old[0][i] = ri.f0; s.old[1][i] = ri.f1; s.old[2][i] = ri.f2;
-                        s.old[3][i] = ri.f3; s.old[4][i] = ri.f4; s.old[5][i] = ri.f5;
-#pragma unroll
-                        for (int c = 0; c < 6; ++c) s.f[c][i] = f[c];
-                        q.p = stashed ? sm.opred[o0 + o] : predict_raw(ri, itime);
-                        store_pred(s, i, q.p);   // h_p of the active particles stays what the reference leaves there
-                        const CorrOut co = correct_core(s, i, itime, a.eta, q);
-                        const uint32_t qq = i - fj0;
-                        if (qq < R)   // patch the resident copy
-                        {
-                            rs[qq] = itime; rs[RC + qq] = co.x; rs[2 * RC + qq] = co.y; rs[3 * RC + qq] = co.z;
-                            rs[4 * RC + qq] = co.vx; rs[5 * RC + qq] = co.vy; rs[6 * RC + qq] = co.vz;
-#pragma unroll
-                            for (int c = 0; c < 6; ++c) rs[(7 + c) * RC + qq] = f[c];
-                        }
-                        // anext[k] is rewritten a step later, behind every CTA's P3 of this step (see A)
-                        ll_store(a.anext + k, add(itime, co.ndt), tag);
-                    }
+                    else
+                        correct_owned(k, o0 + o, f);
                 }
                 if (o0 + P2_OWN < nown) __syncthreads();   // fs is reused
             }
+            if (a.world > 1 && !bail)
+                for (uint32_t o = w; o < nown; o += PS_W)
+                {
+                    // receive: the world's sums of particle k, added in rank order (every rank gets the same bits)
+                    const uint32_t k = sm.own[o];
+                    const unsigned long long tx = a.prof ? gtimer() : 0ull;
+                    double xv[2] = {0.0, 0.0};
+#pragma unroll
+                    for (int u = 0; u < 2; ++u)
+                    {
+                        const int idx = u * 32 + lane;
+                        if (idx < 6 * a.world)
+                        {
+                            const int r = idx / 6, c = idx % 6;
+                            if (!ll_wait_sys(a.xslot[a.rank] + (((size_t)par * PS_MAX_WORLD + r) * PS_NACT_CAP + k) * 6 + c,
+                                             tag, xv[u], wd, a, 3)) dead = true;
+                        }
+                    }
+                    __syncwarp();
+                    double f[6];
+#pragma unroll
+                    for (int c = 0; c < 6; ++c)
+                    {
+                        double sum = 0.0;
+                        for (int r = 0; r < a.world; ++r)
+                        {
+                            const int idx = r * 6 + c;
+                            const double v0 = __shfl_sync(0xffffffffu, xv[0], idx & 31);
+                            const double v1 = __shfl_sync(0xffffffffu, xv[1], idx & 31);
+                            sum += idx < 32 ? v0 : v1;
+                        }
+                        f[c] = sum;
+                    }
+                    if (a.prof && lane == 0) { atomicAdd(a.prof + 12, gtimer() - tx); atomicAdd(a.prof + 13, 1ull); }
+                    correct_owned(k, o, f);
+                }
         }
         if (__syncthreads_or(dead)) bail = true;
         if (bail) break;
@@ -510,6 +525,110 @@ k_persist2(const Persist2Args a)
         last_itime = itime;
         last_nact = nact;
         ++steps;
+        if (nact <= (uint32_t)PS_T)
+        {
+            // The common case, one corrected particle per thread at most: the same result as the general path below with
+            // five CTA barriers instead of ten (every hand-over has its own shared-memory words).
+            double an1 = INF, cmin1 = INF;
+            uint32_t ccnt1 = 0;
+            const bool mine = (uint32_t)tid < nact;
+            if (mine)
+            {
+                if (!ll_wait(a.anext + tid, tag, an1, wd, a, 4)) dead = true;
+                const uint32_t qs = sm.ilist[tid] - s0;
+                if (qs < Ls) tn[qs] = an1;   // the scan slice's copy of t+dt
+            }
+            if (tid < (int)G)
+            {
+                if (!ll_wait(a.cmin + par * a.gpad + tid, tag, cmin1, wd, a, 5)) dead = true;
+                if (!ll2_wait(a.ccnt + par * a.gpad + tid, tag, ccnt1, wd, a, 5)) dead = true;
+            }
+            GDY_PROF2(6);
+            double m = fmin(an1, cmin1);
+            __syncwarp();
+#pragma unroll
+            for (int off = 16; off; off >>= 1) m = fmin(m, __shfl_xor_sync(0xffffffffu, m, off));
+            if (lane == 0) sm.wmin[w] = m;
+            if (__syncthreads_or(dead)) { bail = true; break; }                                   // barrier 1
+            double tnext = sm.wmin[0];
+#pragma unroll
+            for (int ww = 1; ww < PS_W; ++ww) tnext = fmin(tnext, sm.wmin[ww]);
+            // corrected particles that are due again at tnext (ascending, like ilist) / candidates of the slices whose
+            // minimum is tnext (slice order)
+            const bool da = mine && due_at(tnext, an1);
+            const uint32_t ba = __ballot_sync(0xffffffffu, da);
+            const uint32_t bc = (tid < (int)G && due_at(tnext, cmin1)) ? ccnt1 : 0u;
+            uint32_t incl = bc;
+#pragma unroll
+            for (int off = 1; off < 32; off <<= 1)
+            {
+                const uint32_t v = __shfl_up_sync(0xffffffffu, incl, off);
+                if (lane >= off) incl += v;
+            }
+            if (lane == 31) sm.wb[w] = incl;
+            if (lane == 0) sm.wa[w] = __popc(ba);
+            if (tid == 0) sm.big = 0;
+            __syncthreads();                                                                      // barrier 2
+            uint32_t aoff = 0, na = 0, boff = 0, nb = 0;
+#pragma unroll
+            for (int ww = 0; ww < PS_W; ++ww)
+            {
+                if (ww < w) { aoff += sm.wa[ww]; boff += sm.wb[ww]; }
+                na += sm.wa[ww]; nb += sm.wb[ww];
+            }
+            const uint32_t nnext = na + nb;
+            stop_end = steps >= a.max_steps || !(last_itime < a.t_stop);
+            if (cta == 0 && tid == 0) a.trace[steps - 1] = TraceRec{itime, nact, (uint32_t)(gtimer() - t_start)};
+            const uint32_t mycand = boff + incl - bc;   // where this slice's candidates go in listb
+            const uint32_t myold = mine ? sm.ilist[tid] : 0u;
+            itime = tnext;
+            nact = nnext;
+            if (stop_end || nnext == 0 || nnext > a.nact_max) break;
+            if (da) sm.u.l.lista[aoff + __popc(ba & ((1u << lane) - 1u))] = myold;
+            if (tid < (int)G) sm.cnt[tid] = mycand;
+            if (tid == 0) { sm.cnt[G] = nb; sm.nown = 0; }
+            if (bc)
+            {
+                // most candidate lists hold one or two particles: the slice's own thread fetches those; longer lists
+                // are finished by whole warps behind the barrier
+                const uint2 *src = a.clist + ((size_t)par * G + tid) * a.lcap;
+                uint32_t v0 = 0, v1 = 0;
+                if (!ll2_wait(src, tag, v0, wd, a, 6)) dead = true;
+                if (bc > 1 && !ll2_wait(src + 1, tag, v1, wd, a, 6)) dead = true;
+                sm.u.l.listb[mycand] = v0;
+                if (bc > 1) sm.u.l.listb[mycand + 1] = v1;
+                if (bc > 2) sm.big = 1;
+            }
+            if (__syncthreads_or(dead)) { bail = true; break; }                                   // barrier 3
+            if (sm.big)
+            {
+                for (uint32_t c2 = w; c2 < G; c2 += PS_W)
+                {
+                    const uint32_t off = sm.cnt[c2], cc = sm.cnt[c2 + 1] - off;
+                    const uint2 *src = a.clist + ((size_t)par * G + c2) * a.lcap;
+                    for (uint32_t p = 2 + lane; p < cc; p += 32)
+                    {
+                        uint32_t v;
+                        if (!ll2_wait(src + p, tag, v, wd, a, 6)) dead = true;
+                        sm.u.l.listb[off + p] = v;
+                    }
+                }
+                if (__syncthreads_or(dead)) { bail = true; break; }
+            }
+            for (uint32_t e = tid; e < na; e += PS_T)
+            {
+                const uint32_t v = sm.u.l.lista[e];
+                sm.ilist[e + lower_bound_u32(sm.u.l.listb, nb, v)] = v;
+            }
+            for (uint32_t e = tid; e < nb; e += PS_T)
+            {
+                const uint32_t v = sm.u.l.listb[e];
+                sm.ilist[e + lower_bound_u32(sm.u.l.lista, na, v)] = v;
+            }
+            __syncthreads();                                                                      // barrier 4
+            GDY_PROF2(7);
+            continue;
+        }
         double an[PS_NACT_CAP / PS_T];
 #pragma unroll
         for (int q = 0; q < PS_NACT_CAP / PS_T; ++q)
@@ -588,7 +707,7 @@ k_persist2(const Persist2Args a)
     // (src/include/Hermite4.cpp:63-84); the host re-runs the scheduler if it goes on.
     if (!bail && !stop_end)
     {
-        const uint32_t tag = a.tag0 + steps + 1;   // the host skips this tag
+        tag = a.tag0 + steps + 1;   // the host skips this tag
         const uint32_t b0 = min((uint32_t)w * per, Ls), b1 = min(b0 + per, Ls);
         uint32_t c = 0;
         for (uint32_t q0 = b0; q0 < b1; q0 += 32)

@@ -184,29 +184,31 @@ int gdy_predict_timed(gdy_ctx *ctx, double itime, float *ms_out);
 /* Force-kernel variant override for tuning (-1 = heuristic). */
 int gdy_set_tuning(gdy_ctx *ctx, int variant, int jsplit);
 
-/* Small active sets (nact <= nact_max) are stepped by ONE persistent cooperative kernel per run of
- * consecutive small blocks inside gdy_run: predictor fused into the force evaluation, corrector and
- * scheduler behind grid barriers, no host round trip per block step (replaces, for those steps, the
- * per-step launch sequence of the reference: src/include/gpu/Hermite4GPU_integration.cpp:81-124).
- * nact_max: 0 = off, < 0 = default (512), at most 2048.  Sharded contexts need gdy_peer_attach first. */
+/* Small active sets (nact <= nact_max) are stepped by ONE persistent cooperative kernel per run of consecutive small
+ * blocks inside gdy_run, without the host (replaces, for those steps, the per-step launch sequence of the reference:
+ * src/include/gpu/Hermite4GPU_integration.cpp:81-124).  Every CTA owns a slice of the particles, keeps its raw state
+ * resident in shared memory and talks to the other CTAs through flagged slots only: no grid barrier, no fence
+ * (csrc/gdy_persist2.cuh).  Every poll in it is bounded by a watchdog (environment GDY_SPIN_TIMEOUT_MS, default 2000):
+ * a dead or missing peer makes gdy_run return GDY_ERR_STATE instead of hanging.
+ * nact_max: 0 = off, < 0 = default, at most 2048.  Sharded contexts need gdy_peer_attach first. */
 int gdy_set_persist(gdy_ctx *ctx, int nact_max);
 int gdy_persist_stats(const gdy_ctx *ctx, uint64_t *launches_out, uint64_t *steps_out);
-/* ns per phase of that kernel seen by CTA 0 (P1a, P1b, barrier 1, P2, barrier 2, P3, exit, ...); all zero
- * unless GDY_PERSIST_PROF=1 was in the environment at gdy_create (measurement aid). */
+/* ns per phase of that kernel seen by CTA 0 (slots 0-8: load, publish, predict+scan, wait for the active particles,
+ * pair sums, owners' correction, wait for the corrected, lists, exit; 12/13: summed exchange wait of the owner warps
+ * and their count); all zero unless GDY_PERSIST_PROF=1 was in the environment at gdy_create (measurement aid). */
 int gdy_persist_profile(gdy_ctx *ctx, uint64_t *ns_out /* [144] */);
 
-/* Peer memory for the sharded persistent path.  With world > 1 the per-shard force sums of a small block
- * are exchanged INSIDE the persistent kernel: every rank stores its sum as flagged 16-byte slots straight
- * into every peer's buffer over NVLink and adds the world's sums in rank order (bit-identical on all
- * ranks) — no NCCL call, no launch, no host (replaces the host-side sum over GPUs of the reference,
- * src/include/gpu/Hermite4GPU.cu:512-530, for those steps; big blocks keep ncclAllReduce).
+/* Peer memory for the sharded paths.  With world > 1 the per-shard force sums are exchanged without NCCL for every
+ * block of up to 16384 active particles: every rank stores its sums as flagged 16-byte slots straight into every
+ * peer's buffer over NVLink and adds the world's sums in rank order (bit-identical on all ranks) — inside the
+ * persistent kernel for small blocks, as k_xsend + a receive fused into the corrector for mid blocks (replaces the
+ * host-side sum over GPUs of the reference, src/include/gpu/Hermite4GPU.cu:512-530; bigger blocks keep
+ * ncclAllReduce).
  *   gdy_peer_export: handle of THIS context's exchange buffer (GDY_PEER_HANDLE_BYTES bytes);
  *   gdy_peer_attach: all `world` handles in rank order, gathered by the caller (MPI, torch.distributed,
- *                    a vector in the one-process-many-threads host program).  Same process: peer access;
- *                    other processes: CUDA IPC.  Switches the persistent path on for this shard.
- * Blocks of <= 16 active particles (environment GDY_REPL_NACT at gdy_peer_attach, 0 = never) are not exchanged
- * at all: every rank evaluates them against all N j-particles, as a one-GPU run would — one pass over N from L2
- * costs less than a pass over N/world plus the NVLink round trip, and the ranks stay bit-identical. */
+ *                    a vector in the one-process-many-threads host program).  Same process: peer access (same
+ *                    device: the same address space — two logical ranks on one GPU, used by the tests);
+ *                    other processes: CUDA IPC.  Switches the persistent path on for this shard. */
 #define GDY_PEER_HANDLE_BYTES 128
 int gdy_peer_export(gdy_ctx *ctx, uint8_t *handle_out);
 int gdy_peer_attach(gdy_ctx *ctx, const uint8_t *handles);

@@ -60,14 +60,13 @@ def _two_gpu_available():
 
 
 @pytest.mark.skipif(not _two_gpu_available(), reason="needs 2 GPUs")
-@pytest.mark.parametrize("peers,repl", [(False, None), (True, 0), (True, 16)])
-def test_two_real_shards_nccl(H, peers, repl, monkeypatch):
+@pytest.mark.parametrize("peers,xmid", [(False, None), (True, "1"), (True, "0")])
+def test_two_real_shards_nccl(H, peers, xmid, monkeypatch):
     """peers = False: every block step through the per-hook kernels + ncclAllReduce.  peers = True: small
-    blocks through the persistent kernel with the fused NVLink exchange (peer memory), big ones as before;
-    repl = blocks of <= repl active particles are evaluated against all N on every rank, without exchange
-    (0: never), so exchanged and replicated steps alternate inside one launch."""
-    if repl is not None:
-        monkeypatch.setenv("GDY_REPL_NACT", str(repl))
+    blocks through the persistent kernel with the fused NVLink exchange (peer memory); the blocks above its cap
+    through the peer-memory exchange fused into the corrector (xmid = "1") or through ncclAllReduce ("0")."""
+    if xmid is not None:
+        monkeypatch.setenv("GDY_XMID", xmid)
     n, nsteps = 3000, 300 if peers else 60
     m, r, v = plummer(n, seed=8)
     single = H(m, r, v)
@@ -177,7 +176,8 @@ def _run_two_logical_ranks(H, m, r, v, nsteps, nact_max=None, only_rank=None, t_
     return out, err
 
 
-@pytest.mark.parametrize("n,nsteps,nact_max", [(3000, 500, None), (3000, 300, 2048), (12000, 250, None), (640, 400, 64)])
+@pytest.mark.parametrize("n,nsteps,nact_max", [(3000, 500, None), (3000, 300, 2048), (12000, 250, None), (640, 400, 64),
+                                               (12000, 250, 2048)])   # > 16 owned particles per CTA: send-all-then-receive
 def test_two_logical_ranks_one_device(H, monkeypatch, n, nsteps, nact_max):
     import torch
     sms = torch.cuda.get_device_properties(0).multi_processor_count

@@ -3,10 +3,13 @@
 
 Model measured with tools/fp64_mix.cu and tools/fp64_reuse.cu on a B200: an FP64-pipe instruction (DADD, DMUL,
 DFMA, DSETP) costs 2.0 scheduler cycles per warp, unless it reads THREE distinct register pairs from the register
-file, then 2.96 (calibrated on six patterns of tools/fp64_reuse.cu, profiles/r01_fp64_reuse_v9.md).  An operand that the previous instruction of the warp left in the operand reuse cache (`.reuse`
+file, then 2.96 (calibrated on six patterns of tools/fp64_reuse.cu, profiles/archive/r01_fp64_reuse_v9.md).  An operand that the previous instruction of the warp left in the operand reuse cache (`.reuse`
 on the same register in the same slot) is not read from the register file.
 
     python tools/sass_fp64_cost.py gravidy_b200/libgravidy_b200.so k_force_warpILi2ELi4ELi1ELi3ELb0
+    python tools/sass_fp64_cost.py gravidy_b200/libgravidy_b200.so k_force_warpILi2ELi1ELi4ELi3ELb0 4 --list
+        (--list: the loop's SASS, every FP64 instruction marked  "3src" = three distinct register sources,
+         "fed" = one of them comes from the operand reuse cache, "2.96" / "2.00" = modelled cycles)
 """
 import re
 import subprocess
@@ -59,14 +62,16 @@ def regs_of(ins):
     return op, ops[0], ops[1:]
 
 
-def cost(seg, three=2.96, others_flush=True):
+def cost(seg, three=2.96, others_flush=True, marks=None):
     total, n64, n3, n3saved, prev_reuse = 0.0, 0, 0, 0, {}
-    for _, ins in seg:
+    for addr, ins in seg:
         bare = re.sub(r"^@!?U?P\d\s+", "", ins)
         if not bare.startswith(FP64):
             # an instruction in between keeps the cache only if it does not touch the slots; be conservative
             if others_flush:
                 prev_reuse = {}
+            if marks is not None:
+                marks.append((addr, ins, ""))
             continue
         op, dst, srcs = regs_of(ins)
         if op.startswith("DSETP"):
@@ -89,13 +94,17 @@ def cost(seg, three=2.96, others_flush=True):
             if len(read) < 3:
                 n3saved += 1
         total += three if len(read) >= 3 else 2.0
+        if marks is not None:
+            tagm = ("3src " if len(distinct) >= 3 else "     ") + ("fed  " if len(distinct) >= 3 and len(read) < 3 else "     ")
+            marks.append((addr, ins, tagm + ("2.96" if len(read) >= 3 else "2.00")))
         prev_reuse = now_reuse
     return total, n64, n3, n3saved
 
 
 def main():
     path, pat = sys.argv[1], sys.argv[2]
-    pairs = float(sys.argv[3]) if len(sys.argv) > 3 else 0.0
+    pairs = float(sys.argv[3]) if len(sys.argv) > 3 and not sys.argv[3].startswith("-") else 0.0
+    listing = "--list" in sys.argv
     for name, body in functions(path).items():
         if pat not in name:
             continue
@@ -109,6 +118,11 @@ def main():
         msg += (f"; if LDS/MUFU/integer instructions in between do not flush the cache: {n3saved_o} fed, "
                 f"{total_o / (pairs or 1):.2f}")
         print(msg)
+        if listing:
+            marks = []
+            cost(seg, marks=marks)
+            for addr, ins, tagm in marks:
+                print(f"    /*{addr:05x}*/  {tagm:16s} {ins}")
 
 
 if __name__ == "__main__":
