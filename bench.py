@@ -456,6 +456,10 @@ def run_b200(args, m, r, v):
                "block_steps_le_512_active": int(small.sum()), "wall_s_in_block_steps_le_512_active": float(tun[small].sum()) * 1e-6,
                "mean_us_per_block_step_le_512_active": float(tun[small].mean()) if small.any() else None,
                "median_us_per_block_step_nact_le_32": float(np.median(tun[tnn <= 32])) if (tnn <= 32).any() else None,
+               "wall_s_by_nact_bin": {f"{lo + 1}..{hi}": {"block_steps": int(((tnn > lo) & (tnn <= hi)).sum()),
+                                                          "wall_s": float(tun[(tnn > lo) & (tnn <= hi)].sum()) * 1e-6,
+                                                          "pairs": float(tnn[(tnn > lo) & (tnn <= hi)].astype(np.float64).sum()) * n}
+                                      for lo, hi in ((0, 16), (16, 512), (512, 4096), (4096, 16384), (16384, 65536), (65536, n))},
                "persistent_launches": p1[0] - p0[0], "persistent_block_steps": p1[1] - p0[1],
                "launches": h.launch_count() - lb, "exchanges_peer_memory": x1[0] - x0[0], "exchanges_nccl": x1[1] - x0[1]}
         if not args.no_checks:

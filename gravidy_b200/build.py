@@ -14,7 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libgravidy_b200.so")
 SOURCES = ["gdy_ctx.cu"]
-HEADERS = ["gdy_device.cuh", "gdy_force.cuh", "gdy_step.cuh", "gdy_persist.cuh",
+HEADERS = ["gdy_device.cuh", "gdy_force.cuh", "gdy_step.cuh", "gdy_persist.cuh", "gdy_persist2.cuh",
            os.path.join("..", "..", "include", "gravidy_b200.h")]
 
 NVCC_FLAGS = [

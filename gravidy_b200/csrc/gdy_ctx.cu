@@ -1446,20 +1446,19 @@ extern "C" int gdy_force_sweep_full(gdy_ctx *c, int reps, float *ms_out)
     if (reps < 1) return fail(c, GDY_ERR_INVALID, "reps must be >= 1");
     BIND(c);
     if (!c->have_pred) return fail(c, GDY_ERR_STATE, "force_sweep_full before predicted_pos_vel/init_acc_jrk");
-    cudaEvent_t a, b;
-    CU(cudaEventCreate(&a)); CU(cudaEventCreate(&b));
-    CU(cudaEventRecord(a, c->st));
+    // the context's own event pair (force_eval leaves it alone when it is not asked to time): nothing to leak on an
+    // error return
+    CU(cudaEventRecord(c->ev0, c->st));
     const double *buf; uint32_t ld;
     for (int i = 0; i < reps; ++i)
     {
         int r = force_eval(c, c->n, nullptr, &buf, &ld, false);
         if (r) return r;
     }
-    CU(cudaEventRecord(b, c->st));
+    CU(cudaEventRecord(c->ev1, c->st));
     CU(cudaStreamSynchronize(c->st));
     float ms = 0.f;
-    CU(cudaEventElapsedTime(&ms, a, b));
-    cudaEventDestroy(a); cudaEventDestroy(b);
+    CU(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
     if (ms_out) *ms_out = ms / reps;
     return GDY_OK;
 }

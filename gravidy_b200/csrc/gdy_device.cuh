@@ -217,6 +217,18 @@ __device__ __forceinline__ PairCarry pair_head7(double xi, double yi, double zi,
     return c;
 }
 
+// the second half of pair_head7 on its own (form 6 keeps the three DFMAs that share c in a block of their own)
+__device__ __forceinline__ PairCarry pair_carry(const PairMid &p)
+{
+    PairCarry c;
+    c.dx = p.dx; c.dy = p.dy; c.dz = p.dz;
+    c.tx = fma(p.c, p.dx, p.dvx);
+    c.ty = fma(p.c, p.dy, p.dvy);
+    c.tz = fma(p.c, p.dz, p.dvz);
+    c.mr3 = p.mr3;
+    return c;
+}
+
 __device__ __forceinline__ void pair_tail6(Acc6 &s, const PairCarry &p)
 {
     s.ax = fma(p.mr3, p.dx, s.ax);

@@ -28,9 +28,19 @@
 // 3 = software-pipelined: the six-DFMA tails of the previous trip's pairs, which all share m/r^3, issue while this
 // trip's LDS.128 are in flight, then this trip's heads.  tools/force_lab.sh builds them side by side;
 // measured (profiles/archive/r01_force_lab_v9.md): form 3, unroll 1, 512 resident threads is the fastest, 508 Gpairs/s.
+// 6 = form 3 with the instruction groups PINNED (IPT = 2 only, the other shapes keep form 3): every group of FP64
+// instructions that shares an operand — the six-DFMA tail of a pair (m/r^3), the three t = c*d + dv of a pair (c) — sits
+// in a basic block of its own, so ptxas cannot interleave the groups and flags the shared register `.reuse` from one
+// DFMA to the next (a three-source DFMA fed by the operand reuse cache costs 2.0 instead of 2.96 cycles, section 3.1
+// of DESIGN.md).  The block boundaries are labels that a never-taken `goto` ahead of the loop also jumps to (the
+// condition is bits of ld / per_split that are never set, opaque to the compiler): a join point is the one thing
+// ptxas does not schedule across, and it costs no instruction.  Same arithmetic in the same order per accumulator
+// as form 3: bit-identical results.  SASS of the loop: 28 of the 44 three-source DFMAs of a trip fed (form 3: 13),
+// modelled 65.8 instead of 69.4 cycles per pair (tools/sass_fp64_cost.py; profiles/r02_force_lab.md).
 #ifndef GDY_FORCE_FORM
-#define GDY_FORCE_FORM 3
+#define GDY_FORCE_FORM 6
 #endif
+#define GDY_FORM_PIPE (GDY_FORCE_FORM == 3 || GDY_FORCE_FORM == 6)
 #ifndef GDY_FORCE_UNROLL
 #define GDY_FORCE_UNROLL 1
 #endif
@@ -120,12 +130,102 @@ k_force_warp(const ForceArgs a)
         acc[q] = Acc6{0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
     }
     const double e2 = a.e2;
-#if GDY_FORCE_FORM == 3
+#if GDY_FORM_PIPE
     PairCarry pc[2 * IPT];
 #pragma unroll
     for (int q = 0; q < 2 * IPT; ++q) pc[q] = PairCarry{0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
 #endif
 
+#if GDY_FORCE_FORM == 6
+    if constexpr (IPT == 2)
+    {
+        // everything the never-taken entries could reach is initialised: no undefined value on any path
+        double2 X = make_double2(0.0, 0.0), Y = X, Z = X, VX = X, VY = X, VZ = X, M = X;
+        PairMid pm[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) pm[q] = PairMid{0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+        const double *b = myring;
+        int t = 0, jj = 0;
+        // never set (ld <= 2^28, per_split <= 2^24): the entries below exist to make every label a join point
+        const uint32_t opq = (a.ld >> 29) | ((a.per_split >> 25) << 3);
+        if (nt > 0)
+        {
+            mbar_wait(&myfull[0], 0u);
+            if (opq & 0x001u) goto G_LX;
+            if (opq & 0x002u) goto G_T1;
+            if (opq & 0x004u) goto G_LV;
+            if (opq & 0x008u) goto G_T2;
+            if (opq & 0x010u) goto G_LM;
+            if (opq & 0x020u) goto G_T3;
+            if (opq & 0x040u) goto G_HEAD;
+            if (opq & 0x080u) goto G_C0;
+            if (opq & 0x100u) goto G_C1;
+            if (opq & 0x200u) goto G_C2;
+            if (opq & 0x400u) goto G_C3;
+            for (;;)
+            {
+                // tails of the previous trip's four pairs, the loads of this trip's j pair dealt out between them (a
+                // tail frees seven doubles of carry, the next loads land in them: no register pressure peak)
+                pair_tail6(acc[0], pc[0]);
+            G_LX:
+                X = *reinterpret_cast<const double2 *>(b + 0 * JB + jj);
+                Y = *reinterpret_cast<const double2 *>(b + 1 * JB + jj);
+                Z = *reinterpret_cast<const double2 *>(b + 2 * JB + jj);
+            G_T1:
+                pair_tail6(acc[1], pc[1]);
+            G_LV:
+                VX = *reinterpret_cast<const double2 *>(b + 3 * JB + jj);
+                VY = *reinterpret_cast<const double2 *>(b + 4 * JB + jj);
+                VZ = *reinterpret_cast<const double2 *>(b + 5 * JB + jj);
+            G_T2:
+                pair_tail6(acc[0], pc[2]);
+            G_LM:
+                M = *reinterpret_cast<const double2 *>(b + 6 * JB + jj);
+            G_T3:
+                pair_tail6(acc[1], pc[3]);
+            G_HEAD:
+                // heads: differences, r^2, r.v, rsqrt, m/r^3, c — four independent chains for ptxas to interleave
+#pragma unroll
+                for (int q = 0; q < 2; ++q)
+                    pm[q] = pair_head<MASK>(ri[q].x, ri[q].y, ri[q].z, ri[q].vx, ri[q].vy, ri[q].vz, X.x, Y.x, Z.x,
+                                            VX.x, VY.x, VZ.x, M.x, e2);
+#pragma unroll
+                for (int q = 0; q < 2; ++q)
+                    pm[2 + q] = pair_head<MASK>(ri[q].x, ri[q].y, ri[q].z, ri[q].vx, ri[q].vy, ri[q].vz, X.y, Y.y, Z.y,
+                                                VX.y, VY.y, VZ.y, M.y, e2);
+            G_C0:
+                pc[0] = pair_carry(pm[0]);   // t = c*d + dv: three DFMAs that share c
+            G_C1:
+                pc[1] = pair_carry(pm[1]);
+            G_C2:
+                pc[2] = pair_carry(pm[2]);
+            G_C3:
+                pc[3] = pair_carry(pm[3]);
+                jj += 2;
+                if (jj < JB) continue;
+                jj = 0;
+                __syncwarp();   // every lane is done with this stage -> it may be refilled
+                if (lane == 0 && t + NST < nt)
+                {
+                    fence_proxy_async_smem();
+                    issue(t + NST);
+                }
+                if (++t >= nt) break;
+                const int s = t % NST;
+                mbar_wait(&myfull[s], (uint32_t)(t / NST) & 1u);
+                b = myring + (size_t)s * JBD;
+            }
+            // The last trip's tails, HERE and not with the common drain below: nvcc 12.9 drops that drain for this
+            // branch (it is gone from the PTX when the values come out of the multi-entry loop; found by
+            // tools/lab/force_probe.py: the last two j of every warp's last tile contributed nothing).  The carries are
+            // zeroed so that the common drain adds exactly 0.
+            pair_tail6(acc[0], pc[0]); pair_tail6(acc[1], pc[1]); pair_tail6(acc[0], pc[2]); pair_tail6(acc[1], pc[3]);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) pc[q] = PairCarry{0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+        }
+    }
+    else
+#endif
     for (int t = 0; t < nt; ++t)
     {
         const int s = t % NST;
@@ -141,7 +241,7 @@ k_force_warp(const ForceArgs a)
             const double2 VY = *reinterpret_cast<const double2 *>(b + 4 * JB + jj);
             const double2 VZ = *reinterpret_cast<const double2 *>(b + 5 * JB + jj);
             const double2 M = *reinterpret_cast<const double2 *>(b + 6 * JB + jj);
-#if GDY_FORCE_FORM == 3
+#if GDY_FORM_PIPE
             // software pipeline: the six-DFMA tails of the previous trip's pairs issue while this trip's LDS.128
             // are in flight, then this trip's heads
 #pragma unroll
@@ -186,7 +286,7 @@ k_force_warp(const ForceArgs a)
         }
     }
 
-#if GDY_FORCE_FORM == 3
+#if GDY_FORM_PIPE
 #pragma unroll
     for (int q = 0; q < 2 * IPT; ++q) pair_tail6(acc[q % IPT], pc[q]);
 #endif

@@ -99,6 +99,37 @@ def test_every_force_variant_matches_oracle(H, O):
     h.set_tuning(-1, -1)
 
 
+@pytest.mark.parametrize("variant,n,jsplit", [(2, 512, 1), (2, 1280, 2), (0, 768, 1), (3, 384, 1)])
+def test_warp_kernels_see_every_j_position(H, variant, n, jsplit):
+    """One massive j at a time, every position of every tile, all i, against the closed form: a pair that the
+    software-pipelined inner loop drops or doubles (first / last trip of a tile, last tile of a warp, the drain
+    behind the loop) shows up as a j whose pull is missing.  Linearity in the masses makes this exhaustive."""
+    rng = np.random.default_rng(1)
+    r, v = rng.standard_normal((n, 3)), rng.standard_normal((n, 3))
+    eps = 1e-4
+    h = H(np.zeros(n), r, v, softening=eps)
+    h.set_tuning(variant, jsplit)
+    r4, v4 = np.zeros((n, 4)), np.zeros((n, 4))
+    r4[:, :3], v4[:, :3] = r, v
+    bad = []
+    for j in range(n):
+        r4[:, 3] = 0.0
+        r4[j, 3] = 1.0
+        h.upload_particles(r4, v4)
+        h.init_acc_jrk()
+        f = h.download_forces()
+        d, dv = r[j] - r, v[j] - v
+        r2 = (d * d).sum(1) + eps * eps
+        acc = d / r2[:, None] ** 1.5
+        jrk = dv / r2[:, None] ** 1.5 - 3.0 * ((d * dv).sum(1) / r2 ** 2.5)[:, None] * d
+        ea = np.abs(f[:, :3] - acc).max() / np.abs(acc).max()
+        ej = np.abs(f[:, 3:] - jrk).max() / np.abs(jrk).max()
+        if ea > 1e-12 or ej > 1e-12:
+            bad.append(j)
+    h.close()
+    assert not bad, bad
+
+
 def test_zero_softening_masks_self_pair(H, O):
     n = 300
     m, r, v = plummer(n, seed=9)
