@@ -585,8 +585,13 @@ int pick_variant(const gdy_ctx *c, uint32_t nact)
     // j across lanes straight from L2 has the lower fixed cost (no pipeline fill, no second launch);
     // it wins while the whole evaluation is a few tens of microseconds
     if (nact <= 160 || (uint64_t)nact * nj <= 12000000ull) return FV_LANE_I1x4;
-    // the smallest i-tile of the TMA-ring family at every size: with ~24 waves of small CTAs (plan_force) the
-    // block scheduler balances the SMs dynamically, and a CTA's prologue hides behind its neighbours' FP64 work
+    // A block that cannot fill two waves of 64-i tiles (few i-tiles x few j-blocks: the mid blocks of a sharded run,
+    // 1172 active against an eighth of N = 256k) takes 32-i tiles: twice the CTAs to balance the SMs with
+    // (profiles/r02_sweep_shard_w8.md: 94 instead of 114 us at nact 1172, 66 instead of 78 at 600, even at 2400, 1 % slower
+    // from 4800 on)
+    if ((uint64_t)nact * (c->blk_end - c->blk_begin) < 1000000ull) return FV_WARP_I32;
+    // the smallest i-tile of the two-i-per-lane family at every other size: with ~24 waves of small CTAs (plan_force)
+    // the block scheduler balances the SMs dynamically, and a CTA's prologue hides behind its neighbours' FP64 work
     // (profiles/archive/r01_sweep_split_v11.md: 517 vs 508 Gpairs/s for warp_i256 at full-active N = 256k)
     return FV_WARP_I64;
 }
@@ -625,8 +630,28 @@ ForcePlan plan_force(const gdy_ctx *c, uint32_t nact)
         // decides the time), while per-CTA fixed costs overlap with the other resident CTAs' FP64 work.
         split = cdiv(24u * slots, gx);
         const uint32_t cap = units / 16 > 1 ? units / 16 : 1;
-        if (split > cap) split = cap;
         if (split > 192) split = 192;
+        if (split > cap) split = cap;
+        // The last wave: CTAs of one launch take the same time, so the SMs run in step and what is left over for the
+        // last round decides — 19 i-tiles x 187 splits are 3553 CTAs, 24 rounds of 148 and ONE CTA more (646 us where
+        // 590 would do); 19 x 32 on an eighth of the j-particles are 608 CTAs on 592 slots.  The SM with the most CTAs
+        // has ceil(CTAs / SMs) of them and the FP64 pipe makes their times add up, so of the splits between three
+        // quarters of the target and the target take the one with the smallest  ceil(CTAs / SMs) x j-blocks per CTA  (a CTA alone on
+        // its SM is latency-bound: x 1.7), the larger split on a tie (profiles/r02_sweep_shard_w8.md, r02_sweep_plan.md).
+        {
+            const uint32_t sms = (uint32_t)c->num_sms;
+            uint32_t best = split;
+            double best_cost = 1e300;
+            for (uint32_t sp = split; sp >= 1 && 4 * sp >= 3 * split; --sp)
+            {
+                const uint32_t per = cdiv(units, sp), s2 = cdiv(units, per);
+                if (s2 != sp) continue;   // the same plan as a smaller sp
+                const uint32_t q = cdiv(gx * s2, sms);
+                const double cost = (q == 1 ? 1.7 : (double)q) * ((double)per + 0.5);
+                if (cost < best_cost - 1e-9) { best_cost = cost; best = sp; }
+            }
+            split = best;
+        }
     }
     else if (units > 1)
     {
@@ -699,23 +724,33 @@ int force_eval(gdy_ctx *c, uint32_t nact, const uint32_t *move, const double **o
     ++c->launches;
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return fail(c, GDY_ERR_CUDA, "force kernel %s grid (%u,%u): %s", v.name, p.grid.x, p.grid.y, cudaGetErrorString(e));
+    const bool xmid = c->world > 1 && c->peers_ok && c->use_xmid && nact <= (uint32_t)XMID_LD;
+    XSend xs{};
+    if (xmid)
+    {
+        for (int r = 0; r < c->world; ++r) xs.peer[r] = c->xslot[r] + XBUF_SLOTS;
+        xs.rank = c->rank; xs.world = c->world; xs.tag = ++c->xmid_seq; xs.par = xs.tag & 1u; xs.xld = XMID_LD;
+    }
     double *buf;
+    bool sent = false;
     if (v.kind == 1) buf = s.fsum;            // lane kernels reduce their own j-splits
     else if (p.nsplit > 1)
     {
-        k_reduce_partials<<<cdiv(nact, 32), 256, 0, c->st>>>(s.part, s.fsum, nact, p.ld, p.nsplit);
+        // the reduction over the j-splits and the send half of the exchange in one launch
+        k_reduce_partials<<<dim3(cdiv(nact, 32), 6), 256, 0, c->st>>>(s.part, s.fsum, nact, p.ld, p.nsplit, xs);
         LAUNCHED(c);
         buf = s.fsum;
+        sent = xmid;
     }
     else buf = s.part;
     if (timed) CU(cudaEventRecord(c->ev1, c->st));
-    if (c->world > 1 && c->peers_ok && c->use_xmid && nact <= (uint32_t)XMID_LD)
+    if (xmid)
     {
-        XSend xs{};
-        for (int r = 0; r < c->world; ++r) xs.peer[r] = c->xslot[r] + XBUF_SLOTS;
-        xs.rank = c->rank; xs.world = c->world; xs.tag = ++c->xmid_seq; xs.par = xs.tag & 1u;
-        k_xsend<<<cdiv(nact, 256), 256, 0, c->st>>>(buf, p.ld, nact, xs);
-        LAUNCHED(c);
+        if (!sent)
+        {
+            k_xsend<<<cdiv(nact, 256), 256, 0, c->st>>>(buf, p.ld, nact, xs);
+            LAUNCHED(c);
+        }
         XRecv xr{c->xbuf + XBUF_SLOTS, c->world, xs.tag, xs.par, &c->pin->abort, c->spin_timeout_ns};
         ++c->xmid_count;
         if (xr_out) *xr_out = xr;

@@ -497,43 +497,65 @@ k_force_lane(const ForceArgs a)
 // Replaces k_reduce (reference: src/include/gpu/Hermite4GPU_kernels.cu:226-248).
 // Block = 32 k-lanes x 8 split-warps: coalesced over k, the splits strided over the warps (4 loads in
 // flight per thread) and folded through shared memory in warp order.
+// With `xs.world > 1` the sums also leave for the other GPUs from here: flagged slots into buffer [parity][my rank] of
+// every rank's exchange region over NVLink (the send half of the one-shot exchange, gdy_step.cuh), so that the reduce
+// and the collective are one launch.
+struct XSend
+{
+    uint4 *peer[8];                       // every rank's exchange buffer as seen from this device (XMID_MAXW)
+    int rank, world;                      // world <= 1: nothing is sent
+    uint32_t tag, par;
+    uint32_t xld;                         // slots per (rank, component) row of the exchange region (XMID_LD)
+};
+
+__device__ __forceinline__ void xll_store_sys(uint4 *slot, double v, uint32_t tag)
+{
+    const unsigned long long b = (unsigned long long)__double_as_longlong(v);
+    asm volatile("st.relaxed.sys.global.v4.b32 [%0], {%1, %2, %3, %4};" ::"l"(slot), "r"((uint32_t)b), "r"(tag),
+                 "r"((uint32_t)(b >> 32)), "r"(tag)
+                 : "memory");
+}
+
 __global__ void __launch_bounds__(256)
 k_reduce_partials(const double *__restrict__ part, double *__restrict__ fsum, uint32_t nact,
-                  uint32_t ld, uint32_t nsplit)
+                  uint32_t ld, uint32_t nsplit, const XSend xs)
 {
-    __shared__ double red[8][6][32];
+    // grid (k-blocks of 32, 6 components): one component per CTA, so that a mid-size block with many splits (1172
+    // active particles x 171 splits) is 222 CTAs with two rounds of loads each instead of 37 CTAs with a dozen.  Per
+    // (k, component) the additions happen in the same order as ever: the splits w, w + 8, ... in ascending order in
+    // warp w, then the eight warps in ascending order.
+    __shared__ double red[8][32];
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    const uint32_t k = blockIdx.x * 32 + lane;
-    double acc[6] = {0, 0, 0, 0, 0, 0};
+    const uint32_t k = blockIdx.x * 32 + lane, c = blockIdx.y;
+    double acc = 0.0;
     if (k < nact)
     {
         const size_t stride = (size_t)6 * ld;
+        const double *p = part + (size_t)c * ld + k;
         uint32_t sp = w;
-        for (; sp + 24 < nsplit; sp += 32)
+        for (; sp + 56 < nsplit; sp += 64)
         {
-            double v[4][6];
+            double v[8];
 #pragma unroll
-            for (int u = 0; u < 4; ++u)
+            for (int u = 0; u < 8; ++u) v[u] = p[(size_t)(sp + 8 * u) * stride];
 #pragma unroll
-                for (int c = 0; c < 6; ++c) v[u][c] = part[(size_t)(sp + 8 * u) * stride + (size_t)c * ld + k];
-#pragma unroll
-            for (int u = 0; u < 4; ++u)
-#pragma unroll
-                for (int c = 0; c < 6; ++c) acc[c] += v[u][c];
+            for (int u = 0; u < 8; ++u) acc += v[u];
         }
-        for (; sp < nsplit; sp += 8)
-#pragma unroll
-            for (int c = 0; c < 6; ++c) acc[c] += part[(size_t)sp * stride + (size_t)c * ld + k];
+        for (; sp < nsplit; sp += 8) acc += p[(size_t)sp * stride];
     }
-#pragma unroll
-    for (int c = 0; c < 6; ++c) red[w][c][lane] = acc[c];
+    red[w][lane] = acc;
     __syncthreads();
-    if (w < 6 && k < nact)
+    if (w == 0 && k < nact)
     {
         double sum = 0.0;
 #pragma unroll
-        for (int ww = 0; ww < 8; ++ww) sum += red[ww][w][lane];
-        fsum[(size_t)w * ld + k] = sum;
+        for (int ww = 0; ww < 8; ++ww) sum += red[ww][lane];
+        fsum[(size_t)c * ld + k] = sum;
+        if (xs.world > 1)
+        {
+            const size_t at = (((size_t)xs.par * 8 + xs.rank) * 6 + c) * xs.xld + k;
+            for (int r = 0; r < xs.world; ++r) xll_store_sys(xs.peer[r] + at, sum, xs.tag);
+        }
     }
 }
 

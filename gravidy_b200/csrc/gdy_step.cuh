@@ -256,20 +256,8 @@ struct XRecv
     uint32_t *abort_host;                 // pinned: set when a poll gives up
     unsigned long long timeout_ns;
 };
-struct XSend
-{
-    uint4 *peer[XMID_MAXW];               // every rank's exchange buffer as seen from this device
-    int rank, world;
-    uint32_t tag, par;
-};
-
-__device__ __forceinline__ void xll_store_sys(uint4 *slot, double v, uint32_t tag)
-{
-    const unsigned long long b = (unsigned long long)__double_as_longlong(v);
-    asm volatile("st.relaxed.sys.global.v4.b32 [%0], {%1, %2, %3, %4};" ::"l"(slot), "r"((uint32_t)b), "r"(tag),
-                 "r"((uint32_t)(b >> 32)), "r"(tag)
-                 : "memory");
-}
+// XSend and xll_store_sys: gdy_force.cuh (k_reduce_partials sends as well)
+static_assert(XMID_MAXW == 8, "XSend holds eight peers");
 
 __global__ void __launch_bounds__(256)
 k_xsend(const double *__restrict__ fbuf, uint32_t ld, uint32_t nact, XSend x)

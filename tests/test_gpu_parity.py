@@ -124,8 +124,9 @@ def test_warp_kernels_see_every_j_position(H, variant, n, jsplit):
         jrk = dv / r2[:, None] ** 1.5 - 3.0 * ((d * dv).sum(1) / r2 ** 2.5)[:, None] * d
         ea = np.abs(f[:, :3] - acc).max() / np.abs(acc).max()
         ej = np.abs(f[:, 3:] - jrk).max() / np.abs(jrk).max()
-        if ea > 1e-12 or ej > 1e-12:
-            bad.append(j)
+        if ea > 1e-9 or ej > 1e-9:   # a missing pair is an error of order 1; numpy's own rounding in the jerk's
+            bad.append(j)            # cancellation reaches 1e-12 for the closest pairs
+
     h.close()
     assert not bad, bad
 
