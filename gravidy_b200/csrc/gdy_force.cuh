@@ -69,6 +69,17 @@ struct ForceArgs
 
 struct IReg { double x, y, z, vx, vy, vz; };
 
+// two consecutive doubles from shared memory at byte address sa + OFF: LDS.128 with an immediate offset, so that the
+// seven rows of a j pair hang off ONE address register (every instruction that reads a register competes with the
+// FP64 pipe's operand reads: profiles/r02_force_lab.md)
+template <int OFF>
+__device__ __forceinline__ double2 lds2(uint32_t sa)
+{
+    double2 v;
+    asm volatile("ld.shared.v2.f64 {%0, %1}, [%2+%3];" : "=d"(v.x), "=d"(v.y) : "r"(sa), "n"(OFF) : "memory");
+    return v;
+}
+
 __device__ __forceinline__ IReg load_i(const ForceArgs &a, uint32_t k)
 {
     const uint32_t kc = k < a.nact ? k : a.nact - 1;   // lanes past nact compute a duplicate, never stored
@@ -144,8 +155,10 @@ k_force_warp(const ForceArgs a)
         PairMid pm[4];
 #pragma unroll
         for (int q = 0; q < 4; ++q) pm[q] = PairMid{0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
-        const double *b = myring;
-        int t = 0, jj = 0;
+        // the loop's one induction variable: the shared-memory byte address of this trip's two j (the seven rows sit at
+        // immediate offsets from it), compared with the end of the tile's first row
+        uint32_t sa = smem_u32(myring), send = sa + JB * 8;
+        int t = 0;
         // never set (ld <= 2^28, per_split <= 2^24): the entries below exist to make every label a join point
         const uint32_t opq = (a.ld >> 29) | ((a.per_split >> 25) << 3);
         if (nt > 0)
@@ -168,19 +181,19 @@ k_force_warp(const ForceArgs a)
                 // tail frees seven doubles of carry, the next loads land in them: no register pressure peak)
                 pair_tail6(acc[0], pc[0]);
             G_LX:
-                X = *reinterpret_cast<const double2 *>(b + 0 * JB + jj);
-                Y = *reinterpret_cast<const double2 *>(b + 1 * JB + jj);
-                Z = *reinterpret_cast<const double2 *>(b + 2 * JB + jj);
+                X = lds2<0 * JB * 8>(sa);
+                Y = lds2<1 * JB * 8>(sa);
+                Z = lds2<2 * JB * 8>(sa);
             G_T1:
                 pair_tail6(acc[1], pc[1]);
             G_LV:
-                VX = *reinterpret_cast<const double2 *>(b + 3 * JB + jj);
-                VY = *reinterpret_cast<const double2 *>(b + 4 * JB + jj);
-                VZ = *reinterpret_cast<const double2 *>(b + 5 * JB + jj);
+                VX = lds2<3 * JB * 8>(sa);
+                VY = lds2<4 * JB * 8>(sa);
+                VZ = lds2<5 * JB * 8>(sa);
             G_T2:
                 pair_tail6(acc[0], pc[2]);
             G_LM:
-                M = *reinterpret_cast<const double2 *>(b + 6 * JB + jj);
+                M = lds2<6 * JB * 8>(sa);
             G_T3:
                 pair_tail6(acc[1], pc[3]);
             G_HEAD:
@@ -201,9 +214,8 @@ k_force_warp(const ForceArgs a)
                 pc[2] = pair_carry(pm[2]);
             G_C3:
                 pc[3] = pair_carry(pm[3]);
-                jj += 2;
-                if (jj < JB) continue;
-                jj = 0;
+                sa += 16;
+                if (sa != send) continue;
                 __syncwarp();   // every lane is done with this stage -> it may be refilled
                 if (lane == 0 && t + NST < nt)
                 {
@@ -213,7 +225,8 @@ k_force_warp(const ForceArgs a)
                 if (++t >= nt) break;
                 const int s = t % NST;
                 mbar_wait(&myfull[s], (uint32_t)(t / NST) & 1u);
-                b = myring + (size_t)s * JBD;
+                sa = smem_u32(myring + (size_t)s * JBD);
+                send = sa + JB * 8;
             }
             // The last trip's tails, HERE and not with the common drain below: nvcc 12.9 drops that drain for this
             // branch (it is gone from the PTX when the values come out of the multi-entry loop; found by
