@@ -637,7 +637,7 @@ ForcePlan plan_force(const gdy_ctx *c, uint32_t nact)
         // 590 would do); 19 x 32 on an eighth of the j-particles are 608 CTAs on 592 slots.  The SM with the most CTAs
         // has ceil(CTAs / SMs) of them and the FP64 pipe makes their times add up, so of the splits between three
         // quarters of the target and the target take the one with the smallest  ceil(CTAs / SMs) x j-blocks per CTA  (a CTA alone on
-        // its SM is latency-bound: x 1.7), the larger split on a tie (profiles/r02_sweep_shard_w8.md, r02_sweep_plan.md).
+        // its SM is latency-bound: x 1.7), the larger split on a tie (profiles/r02_sweep_shard_w8.md).
         {
             const uint32_t sms = (uint32_t)c->num_sms;
             uint32_t best = split;
@@ -1163,6 +1163,8 @@ int run_persist(gdy_ctx *c, double itime, uint32_t nact, double t_stop, uint32_t
     a.clist = c->p2_clist; a.ecnt = c->p2_ecnt; a.gpad = c->ps_gpad; a.lcap = PS_NACT_CAP;
     a.off_dyn = c->p2_off_dyn; a.lf_pad = c->p2_lf_pad; a.res_cap = c->p2_res_cap; a.ls_cap = c->p2_ls_cap;
     a.ctl_dev = c->ps_ctl; a.ctl_host = c->ps_ctl_host; a.trace = c->ps_trace_host; a.prof = c->p2_prof;
+    a.prof_nact_max = 0xffffffffu;
+    if (const char *e = getenv("GDY_PERSIST_PROF_NACT")) { const long v = atol(e); if (v > 0) a.prof_nact_max = (uint32_t)v; }
     a.abort_word = c->p2_abort; a.timeout_ns = c->spin_timeout_ns;
     a.rank = c->rank; a.world = c->peers_ok ? c->world : 1;
     for (int r = 0; r < PS_MAX_WORLD; ++r) a.xslot[r] = c->xslot[r];
@@ -1283,7 +1285,10 @@ extern "C" int gdy_peer_attach(gdy_ctx *c, const uint8_t *handles)
         }
     }
     c->peers_ok = true;
-    uint32_t def = PS_DEFAULT_NACT;
+    // on four GPUs and more the launch path's fixed cost per block step (launch chain + exchange, ~80 us) outweighs the
+    // persistent kernel's lower pair rate up to its buffer cap: N = 256k on 8 GPUs to t = 1/8 in 2.041 s with 2048 against
+    // 2.075 s with 512 (profiles/r02_persist_8gpu.md); on one GPU 512 stays (blocks of 513..1024: 622 against 584 us)
+    uint32_t def = c->world >= 4 ? (uint32_t)PS_NACT_CAP : PS_DEFAULT_NACT;
     if (const char *e = getenv("GDY_PERSIST_NACT")) def = (uint32_t)atoi(e);
     if (def > (uint32_t)PS_NACT_CAP) def = PS_NACT_CAP;
     c->ps_nact_max = def;

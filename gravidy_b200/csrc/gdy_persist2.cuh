@@ -64,6 +64,7 @@ struct Persist2Args
     PersistCtl *ctl_dev, *ctl_host;
     TraceRec *trace;
     unsigned long long *prof;  // [P2_NPROF] (NULL = off)
+    uint32_t prof_nact_max;    // only block steps with at most this many active particles are timed (slot 14 counts them)
     uint32_t *abort_word;      // 0 = fine; else (phase << 16 | cta) + 1 of the first poll that gave up
     unsigned long long timeout_ns;
     int rank, world;
@@ -245,8 +246,9 @@ k_persist2(const Persist2Args a)
     const unsigned long long t_start = (cta == 0 && tid == 0) ? gtimer() : 0ull;
     const bool prof = a.prof != nullptr && cta == 0 && tid == 0;
     unsigned long long tp = prof ? gtimer() : 0ull;
+    bool profs = prof;         // this step is timed
 #define GDY_PROF2(slot) \
-    do { if (prof) { const unsigned long long tn_ = gtimer(); sm.prof[slot] += tn_ - tp; tp = tn_; } } while (0)
+    do { if (profs) { const unsigned long long tn_ = gtimer(); sm.prof[slot] += tn_ - tp; tp = tn_; } } while (0)
     if (prof)
         for (int q = 0; q < P2_NPROF; ++q) sm.prof[q] = 0ull;
 
@@ -274,6 +276,8 @@ k_persist2(const Persist2Args a)
     {
         tag = a.tag0 + steps + 1;
         const uint32_t par = tag & 1u;
+        profs = prof && nact <= a.prof_nact_max;
+        if (profs) { tp = gtimer(); sm.prof[14] += 1ull; }
 
         // ---- A: the owners publish the predicted active particles ------------------------------------------------
         // ipub[k] is rewritten a step later, after its owner has been through P3 of this step, which needs the
@@ -484,7 +488,8 @@ k_persist2(const Persist2Args a)
                 {
                     // receive: the world's sums of particle k, added in rank order (every rank gets the same bits)
                     const uint32_t k = sm.own[o];
-                    const unsigned long long tx = a.prof ? gtimer() : 0ull;
+                    const bool xprof = a.prof != nullptr && nact <= a.prof_nact_max;
+                    const unsigned long long tx = xprof ? gtimer() : 0ull;
                     double xv[2] = {0.0, 0.0};
 #pragma unroll
                     for (int u = 0; u < 2; ++u)
@@ -512,7 +517,7 @@ k_persist2(const Persist2Args a)
                         }
                         f[c] = sum;
                     }
-                    if (a.prof && lane == 0) { atomicAdd(a.prof + 12, gtimer() - tx); atomicAdd(a.prof + 13, 1ull); }
+                    if (xprof && lane == 0) { atomicAdd(a.prof + 12, gtimer() - tx); atomicAdd(a.prof + 13, 1ull); }
                     correct_owned(k, o, f);
                 }
         }
@@ -705,6 +710,8 @@ k_persist2(const Persist2Args a)
     // (t+dt of the slice is in shared memory, patched).  When the launch ends on its step budget or on t_stop,
     // State.move keeps the list of the last COMPLETED step instead, as the reference leaves it
     // (src/include/Hermite4.cpp:63-84); the host re-runs the scheduler if it goes on.
+    profs = prof;
+    if (profs) tp = gtimer();
     if (!bail && !stop_end)
     {
         tag = a.tag0 + steps + 1;   // the host skips this tag

@@ -72,6 +72,15 @@ PY
       done
       wait; unset GDY_PERSIST_PROF
       tail -n 30 $O/${TAG}_diag_*.txt;;
+    exp)
+      # exp:<gpus>:<tend>: the persistent kernel's phase profile for tiny steps on every rank, then the persistent cap A/B
+      g=${a1:-8}; T=${a2:-0.125}
+      GDY_PERSIST_PROF=1 GDY_PERSIST_PROF_NACT=16 timeout 300 bash -c "$(declare -f TR); TR $g tools/integrate.py --particles 262144 --tend $T --rank-prof $O/${TAG}_exp_prof16_${g}gpu" > $O/${TAG}_exp_prof16_${g}gpu.json 2> $O/${TAG}_exp_prof16_${g}gpu.err
+      for cap in 512 1024 2048; do
+        GDY_PERSIST_NACT=$cap timeout 300 bash -c "$(declare -f TR); TR $g tools/integrate.py --particles 262144 --tend $T --rank-prof $O/${TAG}_exp_cap${cap}_${g}gpu" > $O/${TAG}_exp_cap${cap}_${g}gpu.json 2> $O/${TAG}_exp_cap${cap}_${g}gpu.err
+        echo "cap $cap: $(python -c "import json;d=json.loads(open('$O/${TAG}_exp_cap${cap}_${g}gpu.json').read().strip().splitlines()[-1]);print('wall',round(d['wall_s'],4),' '.join('%s:%.0f'%(b['nact'][1],b['median_us']) for b in d['bins']))" 2>&1)"
+      done
+      cat $O/${TAG}_exp_prof16_${g}gpu.rank0.txt | head -4;;
     *) echo "unknown stage $st";;
   esac
   echo "[$st] $(( $(date +%s) - t0 )) s"

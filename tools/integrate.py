@@ -110,7 +110,12 @@ def main():
                      "exit", "-", "-", "-", "xchg.wait_total", "xchg.count"]
         with open(f"{a.rank_prof}.rank{rank}.txt", "w") as f:
             f.write(f"rank {rank}/{world} wall {st.wall_ms:.1f} ms steps {st.iterations} persist_steps {ps}\n")
+            if len(prof) > 14 and prof[14]:
+                ps = prof[14]   # the timed steps (GDY_PERSIST_PROF_NACT: only steps with at most that many active particles)
+                f.write(f"timed steps {ps} (nact <= {os.environ.get('GDY_PERSIST_PROF_NACT', 'any')})\n")
             f.write("ns/step by phase (CTA 0): " + "  ".join(f"{nm} {v / ps:.0f}" for nm, v in zip(names, prof) if v) + "\n")
+            if len(prof) > 13 and prof[13]:
+                f.write(f"exchange wait per owned particle: {prof[12] / prof[13]:.0f} ns over {prof[13]} waits\n")
             for b in bins:
                 f.write(f"nact ({b['nact'][0]},{b['nact'][1]}] steps {b['steps']} median_us {b['median_us']:.1f} "
                         f"total_ms {b['share_of_wall'] * tu.sum() / 1e3:.2f}\n")
