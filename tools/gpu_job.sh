@@ -6,6 +6,8 @@
 #   bench[:N]        bench.py on N GPUs (default 1)               benchref  bench.py --impl reference
 #   lat:<n>[:spec]   tools/step_latency.py at n particles         integ:<n>:<tend>[:gpus[:extra env]]  tools/integrate.py
 #   ncu_force        ncu --set full of the force kernel in bench.py (one capture) + launch list
+#   ncu_energy       ncu --set full of k_energy and k_knn_distance at N = 256k
+#   lab[:nacts]      every build under gravidy_b200/lab/*.so against the production library: bits and big-block rates
 #   sanit            compute-sanitizer memcheck + racecheck of a short persistent-kernel run
 #   diag4            the 4-GPU small-step diagnostic of round 2 (phase profile of every rank)
 set -u
@@ -56,6 +58,34 @@ PY
       timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/${TAG}_launches.csv \
         python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-extras > $O/${TAG}_ncu_launches.log 2>&1
       echo "[$st] launches rc=$?";;
+    ncu_energy)
+      # one ncu --set full capture each of the energy and the k-th-neighbour kernels at N = 256k (FP64-bound)
+      cat > /tmp/ncu_energy.py <<'PY'
+import sys; sys.path.insert(0, ".")
+from gravidy_b200.hermite4 import Hermite4B200
+from gravidy_b200.plummer import plummer, default_seed
+n = 262144
+m, r, v = plummer(n, seed=default_seed(n))
+h = Hermite4B200(m, r, v, softening=1e-4, eta=0.01, device=0)
+print("energy ms", h.energy_timed()); print("knn ms", h.neighbour_timed(6))
+PY
+      timeout 900 ncu --set full --clock-control none --import-source on -k regex:'k_energy$|k_knn_distance' -c 2 -o $O/${TAG}_energy_knn \
+        python /tmp/ncu_energy.py > $O/${TAG}_ncu_energy.log 2>&1
+      echo "[$st] rc=$? $(tail -2 $O/${TAG}_ncu_energy.log | tr '\n' ' ')";;
+    lab)
+      # lab[:nacts]: every library build under gravidy_b200/lab/ against the production library: forces bit for bit
+      # (tools/lab/force_cmp.sh) and the big-block rates (tools/sweep_big.py)
+      P=gravidy_b200/libgravidy_b200.so
+      echo "== production" > $O/${TAG}_lab.txt
+      timeout 300 python tools/sweep_big.py --n 262144 --nacts ${a1:-1172,8192,262144} --variants 2 --reps 4 >> $O/${TAG}_lab.txt 2>&1
+      for L in gravidy_b200/lab/*.so; do
+        echo "== $L" >> $O/${TAG}_lab.txt
+        timeout 300 bash tools/lab/force_cmp.sh $P $L 4099 65536 >> $O/${TAG}_lab.txt 2>&1
+        GDY_LIB=$PWD/$L timeout 300 python tools/sweep_big.py --n 262144 --nacts ${a1:-1172,8192,262144} --variants 2 --reps 4 >> $O/${TAG}_lab.txt 2>&1
+      done
+      echo "== production again" >> $O/${TAG}_lab.txt
+      timeout 300 python tools/sweep_big.py --n 262144 --nacts ${a1:-1172,8192,262144} --variants 2 --reps 4 >> $O/${TAG}_lab.txt 2>&1
+      grep -E "^==|differing|^262144" $O/${TAG}_lab.txt;;
     sanit)
       timeout 1200 compute-sanitizer --tool memcheck --error-exitcode 9 python tools/sanitize_smoke.py > $O/${TAG}_sanit_memcheck.log 2>&1
       echo "[$st] memcheck rc=$? $(tail -2 $O/${TAG}_sanit_memcheck.log | tr '\n' ' ')"
