@@ -217,51 +217,6 @@ __device__ __forceinline__ PairCarry pair_head7(double xi, double yi, double zi,
     return c;
 }
 
-// Form 7 splits the head three ways so that the two three-source DFMAs of r.v can be fed as well: (1) the position
-// differences, (2) per pair and in a basic block of its own: the velocity differences and r^2 / r.v INTERLEAVED —
-// r2 = fma(dy, dy, r2) is followed by rv = fma(dy, dvy, rv), which finds dy in the operand reuse cache —, (3) rsqrt,
-// m/r^3 and c.  Same operations on the same operands in the same order per value as pair_head: same bits.
-__device__ __forceinline__ void pair_head_r2rv(PairMid &p, double vxi, double vyi, double vzi, double vxj, double vyj,
-                                               double vzj, double e2, double &r2_out, double &rv_out)
-{
-    p.dvx = vxj - vxi; p.dvy = vyj - vyi; p.dvz = vzj - vzi;
-    double r2 = fma(p.dx, p.dx, e2);
-    double rv = p.dx * p.dvx;
-    r2 = fma(p.dy, p.dy, r2);
-    rv = fma(p.dy, p.dvy, rv);
-    r2 = fma(p.dz, p.dz, r2);
-    rv = fma(p.dz, p.dvz, rv);
-    r2_out = r2; rv_out = rv;
-}
-// the same in three pieces (GDY_FORCE_FORM7 == 2: the y and z steps in basic blocks of their own, because inside one
-// block ptxas hoists the r.v chain above the r^2 chain and the adjacency is lost)
-__device__ __forceinline__ void pair_head_rx(PairMid &p, double vxi, double vyi, double vzi, double vxj, double vyj,
-                                             double vzj, double e2, double &r2, double &rv)
-{
-    p.dvx = vxj - vxi; p.dvy = vyj - vyi; p.dvz = vzj - vzi;
-    r2 = fma(p.dx, p.dx, e2);
-    rv = p.dx * p.dvx;
-}
-__device__ __forceinline__ void pair_head_ry(const PairMid &p, double &r2, double &rv)
-{
-    r2 = fma(p.dy, p.dy, r2);
-    rv = fma(p.dy, p.dvy, rv);
-}
-__device__ __forceinline__ void pair_head_rz(const PairMid &p, double &r2, double &rv)
-{
-    r2 = fma(p.dz, p.dz, r2);
-    rv = fma(p.dz, p.dvz, rv);
-}
-template <bool MASK_SELF>
-__device__ __forceinline__ void pair_head_fin(PairMid &p, double r2, double rv, double mj)
-{
-    double y = rsqrt_f64(r2);
-    if (MASK_SELF) y = (r2 > 0.0) ? y : 0.0;
-    const double y2 = y * y;
-    p.mr3 = (mj * y) * y2;
-    p.c = (rv * y2) * (-3.0);
-}
-
 // the second half of pair_head7 on its own (form 6 keeps the three DFMAs that share c in a block of their own)
 __device__ __forceinline__ PairCarry pair_carry(const PairMid &p)
 {

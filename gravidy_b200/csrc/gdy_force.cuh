@@ -41,10 +41,6 @@
 #define GDY_FORCE_FORM 6
 #endif
 #define GDY_FORM_PIPE (GDY_FORCE_FORM == 3 || GDY_FORCE_FORM == 6)
-// form 6 with the r^2 / r.v of a pair interleaved in a basic block of its own (gdy_device.cuh: pair_head_r2rv)
-#ifndef GDY_FORCE_FORM7
-#define GDY_FORCE_FORM7 0
-#endif
 #ifndef GDY_FORCE_UNROLL
 #define GDY_FORCE_UNROLL 1
 #endif
@@ -104,14 +100,12 @@ k_force_warp(const ForceArgs a)
     uint64_t *full = reinterpret_cast<uint64_t *>(ring + (size_t)NW * NST * JBD);  // [NW][NST]
 
     const int tid = threadIdx.x, lane = tid & 31;
-#ifdef GDY_FORCE_UADDR
-    // the warp index through a warp reduction: ptxas then KNOWS that it (and the ring address, the tile count and the
-    // loop's address arithmetic derived from it) is the same in every lane, keeps them in uniform registers and the
-    // hot loop's LDS.128 [UR + imm] / UIADD3 / UISETP stop reading vector registers
+    // The warp index through a warp reduction (REDUX writes a uniform register): ptxas then KNOWS that it — and the ring
+    // address, the tile count and the loop's address arithmetic derived from it — is the same in every lane, keeps them in
+    // uniform registers, and the hot loop's LDS.128 [UR + imm] / UIADD3 / UISETP / BRA.U stop reading vector registers.
+    // Every instruction that reads a vector register takes an operand-read cycle away from the FP64 pipe: nine of
+    // them per trip gone, 552 instead of 538 Gpairs/s (profiles/r02_force_lab.md).
     const int warp = (int)__reduce_max_sync(0xffffffffu, (unsigned)(tid >> 5));
-#else
-    const int warp = tid >> 5;
-#endif
     const int wi = warp % WI, wj = warp / WI;
     double *myring = ring + (size_t)warp * NST * JBD;
     uint64_t *myfull = full + warp * NST;
@@ -167,19 +161,10 @@ k_force_warp(const ForceArgs a)
         PairMid pm[4];
 #pragma unroll
         for (int q = 0; q < 4; ++q) pm[q] = PairMid{0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
-#if GDY_FORCE_FORM7
-        double hr2[4] = {1.0, 1.0, 1.0, 1.0}, hrv[4] = {0.0, 0.0, 0.0, 0.0};
-#endif
         // the loop's one induction variable: the shared-memory byte address of this trip's two j (the seven rows sit at
         // immediate offsets from it), compared with the end of the tile's first row
-#ifdef GDY_FORCE_UADDR
-        // the ring address is the same in every lane of the warp; a warp reduction tells ptxas so (REDUX writes a uniform
-        // register), and the loop's address arithmetic and its LDS.128 [UR + imm] stop reading vector registers
-        const uint32_t ring_u = smem_u32(myring);
+        const uint32_t ring_u = smem_u32(myring);   // warp-uniform (see `warp` above)
         uint32_t sa = ring_u, send = sa + JB * 8;
-#else
-        uint32_t sa = smem_u32(myring), send = sa + JB * 8;
-#endif
         int t = 0;
         // never set (ld, nact <= 2^28, per_split, jb, je <= 2^24): the entries below exist to make every label a join point
         const uint32_t opq = (a.ld >> 29) | ((a.per_split >> 25) << 3) | ((a.nact >> 29) << 10) | ((a.jb >> 26) << 13) |
@@ -194,23 +179,6 @@ k_force_warp(const ForceArgs a)
             if (opq & 0x010u) goto G_LM;
             if (opq & 0x020u) goto G_T3;
             if (opq & 0x040u) goto G_HEAD;
-#if GDY_FORCE_FORM7
-            if (opq & 0x800u) goto G_R0;
-            if (opq & 0x1000u) goto G_R1;
-            if (opq & 0x2000u) goto G_R2;
-            if (opq & 0x4000u) goto G_R3;
-            if (opq & 0x8000u) goto G_S;
-#if GDY_FORCE_FORM7 == 2
-            if (opq & 0x10000u) goto G_R0Y;
-            if (opq & 0x20000u) goto G_R0Z;
-            if (opq & 0x40000u) goto G_R1Y;
-            if (opq & 0x80000u) goto G_R1Z;
-            if (opq & 0x100000u) goto G_R2Y;
-            if (opq & 0x200000u) goto G_R2Z;
-            if (opq & 0x400000u) goto G_R3Y;
-            if (opq & 0x800000u) goto G_R3Z;
-#endif
-#endif
             if (opq & 0x080u) goto G_C0;
             if (opq & 0x100u) goto G_C1;
             if (opq & 0x200u) goto G_C2;
@@ -237,51 +205,6 @@ k_force_warp(const ForceArgs a)
             G_T3:
                 pair_tail6(acc[1], pc[3]);
             G_HEAD:
-#if GDY_FORCE_FORM7
-                // position differences of the four pairs (two-source DADDs)
-#pragma unroll
-                for (int q = 0; q < 2; ++q)
-                {
-                    pm[q].dx = X.x - ri[q].x; pm[q].dy = Y.x - ri[q].y; pm[q].dz = Z.x - ri[q].z;
-                    pm[2 + q].dx = X.y - ri[q].x; pm[2 + q].dy = Y.y - ri[q].y; pm[2 + q].dz = Z.y - ri[q].z;
-                }
-#if GDY_FORCE_FORM7 == 3
-                // x steps of the four pairs (free order), then ONE block with the y steps and ONE with the z steps
-            G_R0:
-                pair_head_rx(pm[0], ri[0].vx, ri[0].vy, ri[0].vz, VX.x, VY.x, VZ.x, e2, hr2[0], hrv[0]);
-                pair_head_rx(pm[1], ri[1].vx, ri[1].vy, ri[1].vz, VX.x, VY.x, VZ.x, e2, hr2[1], hrv[1]);
-                pair_head_rx(pm[2], ri[0].vx, ri[0].vy, ri[0].vz, VX.y, VY.y, VZ.y, e2, hr2[2], hrv[2]);
-                pair_head_rx(pm[3], ri[1].vx, ri[1].vy, ri[1].vz, VX.y, VY.y, VZ.y, e2, hr2[3], hrv[3]);
-            G_R1:
-                pair_head_ry(pm[0], hr2[0], hrv[0]); pair_head_ry(pm[1], hr2[1], hrv[1]);
-                pair_head_ry(pm[2], hr2[2], hrv[2]); pair_head_ry(pm[3], hr2[3], hrv[3]);
-            G_R2:
-                pair_head_rz(pm[0], hr2[0], hrv[0]); pair_head_rz(pm[1], hr2[1], hrv[1]);
-                pair_head_rz(pm[2], hr2[2], hrv[2]); pair_head_rz(pm[3], hr2[3], hrv[3]);
-            G_R3:
-#else
-#if GDY_FORCE_FORM7 == 2
-#define GDY_R2RV(q, QQ, JJ) \
-            G_R##q: pair_head_rx(pm[q], ri[QQ].vx, ri[QQ].vy, ri[QQ].vz, VX.JJ, VY.JJ, VZ.JJ, e2, hr2[q], hrv[q]); \
-            G_R##q##Y: pair_head_ry(pm[q], hr2[q], hrv[q]); \
-            G_R##q##Z: pair_head_rz(pm[q], hr2[q], hrv[q]);
-#else
-#define GDY_R2RV(q, QQ, JJ) \
-            G_R##q: pair_head_r2rv(pm[q], ri[QQ].vx, ri[QQ].vy, ri[QQ].vz, VX.JJ, VY.JJ, VZ.JJ, e2, hr2[q], hrv[q]);
-#endif
-                GDY_R2RV(0, 0, x)
-                GDY_R2RV(1, 1, x)
-                GDY_R2RV(2, 0, y)
-                GDY_R2RV(3, 1, y)
-#undef GDY_R2RV
-#endif
-            G_S:
-                // rsqrt, m/r^3, c: four independent chains for ptxas to interleave
-                pair_head_fin<MASK>(pm[0], hr2[0], hrv[0], M.x);
-                pair_head_fin<MASK>(pm[1], hr2[1], hrv[1], M.x);
-                pair_head_fin<MASK>(pm[2], hr2[2], hrv[2], M.y);
-                pair_head_fin<MASK>(pm[3], hr2[3], hrv[3], M.y);
-#else
                 // heads: differences, r^2, r.v, rsqrt, m/r^3, c — four independent chains for ptxas to interleave
 #pragma unroll
                 for (int q = 0; q < 2; ++q)
@@ -291,7 +214,6 @@ k_force_warp(const ForceArgs a)
                 for (int q = 0; q < 2; ++q)
                     pm[2 + q] = pair_head<MASK>(ri[q].x, ri[q].y, ri[q].z, ri[q].vx, ri[q].vy, ri[q].vz, X.y, Y.y, Z.y,
                                                 VX.y, VY.y, VZ.y, M.y, e2);
-#endif
             G_C0:
                 pc[0] = pair_carry(pm[0]);   // t = c*d + dv: three DFMAs that share c
             G_C1:
@@ -311,11 +233,7 @@ k_force_warp(const ForceArgs a)
                 if (++t >= nt) break;
                 const int s = t % NST;
                 mbar_wait(&myfull[s], (uint32_t)(t / NST) & 1u);
-#ifdef GDY_FORCE_UADDR
                 sa = ring_u + (uint32_t)s * (JBD * 8);
-#else
-                sa = smem_u32(myring + (size_t)s * JBD);
-#endif
                 send = sa + JB * 8;
             }
             // The last trip's tails, HERE and not with the common drain below: nvcc 12.9 drops that drain for this

@@ -101,6 +101,25 @@ def cost(seg, three=2.96, others_flush=True, marks=None):
     return total, n64, n3, n3saved
 
 
+def other_reg_readers(seg):
+    """Instructions of other pipes that read a vector register (LDS / MUFU / integer with R operands): each takes one
+    operand-read cycle away from the FP64 pipe (profiles/r02_force_lab.md; measured by removing them one by one).  Uniform
+    datapath instructions (UIADD3, UISETP, LDS [UR + imm], BRA.U) and moves of RZ do not."""
+    n = 0
+    for _, ins in seg:
+        bare = re.sub(r"^@!?U?P\d\s+", "", ins)
+        if bare.startswith(FP64) or bare.startswith(("BRA", "NOP", "WARPSYNC", "BSYNC", "BSSY")):
+            continue
+        parts = bare.split(None, 1)
+        if len(parts) < 2:
+            continue
+        ops = [o.strip() for o in parts[1].split(",")]
+        srcs = ops[1:] if not parts[0].startswith(("ST", "RED", "ATOM")) else ops
+        if any(re.search(r"\bR\d+", o) for o in srcs):
+            n += 1
+    return n
+
+
 def main():
     path, pat = sys.argv[1], sys.argv[2]
     pairs = float(sys.argv[3]) if len(sys.argv) > 3 and not sys.argv[3].startswith("-") else 0.0
@@ -117,6 +136,9 @@ def main():
             msg += f" = {total / pairs:.2f} per pair ({n64 / pairs:.1f} FP64 instr per pair)"
         msg += (f"; if LDS/MUFU/integer instructions in between do not flush the cache: {n3saved_o} fed, "
                 f"{total_o / (pairs or 1):.2f}")
+        nother = other_reg_readers(seg)
+        msg += (f"; {nother} instructions of other pipes read a vector register (+1 cycle each): "
+                f"{total + nother:.1f} cycles per trip" + (f" = {(total + nother) / pairs:.2f} per pair" if pairs else ""))
         print(msg)
         if listing:
             marks = []
