@@ -40,7 +40,7 @@ sys.path.insert(0, ROOT)
 FLOP_PER_PAIR = 60.0
 METRIC = "hermite_fp64_gflops_60flop_per_pair_N256k"
 UNIT = "GFLOP/s"
-NCU_DRAM_BYTES_PER_LAUNCH = 14995712 + 2934272   # profiles/r01_force_warp_ncu_v12.md
+NCU_DRAM_BYTES_PER_LAUNCH = 14928384 + 3308544   # profiles/r02_force_warp_ncu.md
 
 
 def parse_args():
@@ -332,16 +332,21 @@ def run_b200(args, m, r, v):
         # ---- the other two FP64-bound kernels of SURVEY 8(d): energy and the k-th neighbour search ----------
         if hasattr(h, "energy_timed"):
             roofline_energy = {}
-            for nm, fn, instr in (("k_energy", h.energy_timed, 12.0), ("k_knn_distance", lambda: h.neighbour_timed(6), 9.0)):
+            # k_energy is i-sharded over the ranks (each rank: its i-chunks x all j); the k-th-neighbour search serves the
+            # host program's density centre on the rank that writes the log and is NOT sharded: every rank runs all N x N
+            for nm, fn, instr, sharded in (("k_energy", h.energy_timed, 12.0, True),
+                                           ("k_knn_distance", lambda: h.neighbour_timed(6), 9.0, False)):
                 fn()
                 tms = float(np.mean([fn() for _ in range(3)]))
+                mine = pairs / world if sharded else pairs
                 # the FP64 pipe retires 64 lanes per clock per SM: instr / pair against the DFMA peak's instruction rate
-                ach = pairs / world * instr / (tms * 1e-3) / 1e12      # T(FP64 instr)/s
+                ach = mine * instr / (tms * 1e-3) / 1e12               # T(FP64 instr)/s of this rank
                 pk = peak_tf / 2.0                                      # the peak in DFMA instructions (2 flop each)
                 roofline_energy[nm] = {"bound": "fp64", "ms_per_launch": tms, "fp64_instr_per_ordered_pair": instr,
                                        "achieved": ach, "peak": pk, "unit": "T FP64 instr/s", "frac": ach / pk,
-                                       "pairs_per_s": pairs / world / (tms * 1e-3),
-                                       "i_slice": f"rank's slice of {n // world} i-particles x all {n} j" if world > 1 else "all N x N"}
+                                       "pairs_per_s": mine / (tms * 1e-3),
+                                       "i_slice": (f"rank's slice of {n // world} i-particles x all {n} j"
+                                                   if world > 1 and sharded else "all N x N")}
 
     # ---- e2e: host buffers through the C ABI, copies inside the timed region --------------------------
     r4 = torch.empty((n, 4), dtype=torch.float64).pin_memory().numpy()
@@ -546,7 +551,7 @@ def run_b200(args, m, r, v):
                          "traffic": NCU_DRAM_BYTES_PER_LAUNCH if (n == 262144 and world == 1) else None,
                          "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of one ncu --set full "
                                            "capture of this kernel at N=262144 on 1 GPU "
-                                           "(profiles/r01_force_warp_ncu_v12.md): 15.00 MB + 2.93 MB; "
+                                           "(profiles/r02_force_warp_ncu.md): 14.93 MB + 3.31 MB; "
                                            "algorithmic 14.7 MB in + 12.6 MB out",
                          "kernel": "k_force_warp<IPT=2,WI=1,WJ=4,NST=3> (warp_i64, 24 waves of CTAs)",
                          "peak_source": "DFMA micro-benchmark on this GPU (gdy_measure_fp64_peak); "

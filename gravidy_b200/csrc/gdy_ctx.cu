@@ -12,6 +12,7 @@
 #include "gdy_persist.cuh"
 #include "gdy_persist2.cuh"
 
+#include <atomic>
 #include <chrono>
 #include <cmath>
 #include <cstdarg>
@@ -854,6 +855,27 @@ int launch_sched(gdy_ctx *c, double itime, bool from_min)
     return 0;
 }
 
+// Wait for the scheduler's {ITIME, nact} of launch_sched: the kernel writes the pinned slot with `seq` last (block 0, as
+// soon as the counts are summed), so the host polls the slot instead of waiting for the stream to drain — the remaining
+// blocks only write the active list, which the next launches see in stream order.  cudaStreamQuery every few hundred
+// polls catches a failed launch (the slot would never arrive).
+int wait_sched(gdy_ctx *c)
+{
+    volatile SchedOut *so = &c->pin->sched;
+    for (uint32_t spin = 0; so->seq != c->seq; ++spin)
+    {
+        if ((spin & 255u) == 255u)
+        {
+            const cudaError_t q = cudaStreamQuery(c->st);
+            if (q == cudaErrorNotReady) continue;
+            if (q != cudaSuccess) return fail(c, GDY_ERR_CUDA, "block step: %s", cudaGetErrorString(q));
+            if (so->seq != c->seq) return fail(c, GDY_ERR_STATE, "the scheduler kernel left no result (seq %u != %u)", so->seq, c->seq);
+        }
+    }
+    std::atomic_thread_fence(std::memory_order_acquire);
+    return 0;
+}
+
 int launch_min_time(gdy_ctx *c)
 {
     k_min_time<<<c->n_min_blocks, 256, 0, c->st>>>(c->s, c->n, c->d_block_min);
@@ -1410,13 +1432,21 @@ extern "C" int gdy_run(gdy_ctx *c, double atime, double itime0, double t_stop, u
             LAUNCHED(c);
         }
         else if ((r = launch_sched(c, 0.0, true))) return r;
-        CU(cudaStreamSynchronize(c->st));
+        if (last) CU(cudaStreamSynchronize(c->st));
+        else if ((r = wait_sched(c))) return r;
         if ((r = check_abort(c))) return r;
         ATIME = last ? c->pin->atime : c->pin->sched.itime;
         if (timed && nact)
         {
             float ms = 0.f;
-            CU(cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+            cudaError_t ee = cudaEventElapsedTime(&ms, c->ev0, c->ev1);
+            if (ee == cudaErrorNotReady)   // the slot can be ahead of the event's own completion record
+            {
+                (void)cudaGetLastError();
+                CU(cudaEventSynchronize(c->ev1));
+                ee = cudaEventElapsedTime(&ms, c->ev0, c->ev1);
+            }
+            CU(ee);
             force_ms += ms;
         }
         if (it < trace_cap)

@@ -140,9 +140,10 @@ void Hermite4B200::next_integration_time(double &ATIME)
 
 double Hermite4B200::get_energy_gpu()
 {
-    double ek = 0.0, ep = 0.0;
-    check(gdy_energy(shards[0], &ek, &ep), 0, "gdy_energy");
-    return ek + ep;
+    // collective on a sharded run: every rank sums its i-chunks and the chunk sums are all-reduced (same bits on every rank)
+    std::vector<double> ek(ngpus, 0.0), ep(ngpus, 0.0);
+    each_shard([&](int g) { check(gdy_energy(shards[g], &ek[g], &ep[g]), g, "gdy_energy"); });
+    return ek[0] + ep[0];
 }
 
 void Hermite4B200::refresh_mirrors(bool forces)

@@ -93,8 +93,22 @@ def test_force_kernel_fp64_instruction_budget():
         assert n3 == 11 * pairs, (n3, pairs)
         assert fed >= 2 * pairs, (fed, pairs)
         assert total / pairs < 72.6                          # below the nothing-fed bound
+        # round 2: the pinned groups feed at least 6 of the 11 three-source DFMAs of a pair, and the loop's addressing
+        # sits in uniform registers (LDS.128 [UR + imm], UIADD3, UISETP): only the MUFU seeds still read a vector register
+        assert fed >= 6 * pairs, (fed, pairs)
+        assert S.other_reg_readers(seg) <= pairs, S.other_reg_readers(seg)
+        assert any(re.match(r"LDS\.128 R\d+, \[UR\d+", i) for _, i in seg), "the hot loop's loads no longer use a uniform address"
         txt = "\n".join(i for _, i in fns[name[0]])
         assert "UBLKCP" in txt and "MUFU.RSQ64H" in txt and "SYNCS" in txt   # TMA bulk copy, SFU seed, mbarrier
+
+
+def test_host_program_calls_collective_hooks_on_every_shard():
+    """gdy_energy, the force hooks, the uploads and gdy_run are COLLECTIVE on a sharded run (NCCL or peer exchange
+    inside): the host program must call them on every shard, never on shards[0] alone (a -g 2 run hung in the first
+    energy evaluation that way).  Only downloads and the k-th-neighbour search may address one shard."""
+    src = open(os.path.join(ROOT, "gravidy_b200", "host", "Hermite4B200.cpp")).read()
+    single = set(re.findall(r"(gdy_\w+)\(shards\[0\]", src))
+    assert single <= {"gdy_neighbour_distance", "gdy_download_forces", "gdy_download_state"}, single
 
 
 @pytest.mark.parametrize("world", [1, 2, 3, 8])

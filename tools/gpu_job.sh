@@ -69,9 +69,11 @@ m, r, v = plummer(n, seed=default_seed(n))
 h = Hermite4B200(m, r, v, softening=1e-4, eta=0.01, device=0)
 print("energy ms", h.energy_timed()); print("knn ms", h.neighbour_timed(6))
 PY
-      timeout 900 ncu --set full --clock-control none --import-source on -k regex:'k_energy$|k_knn_distance' -c 2 -o $O/${TAG}_energy_knn \
-        python /tmp/ncu_energy.py > $O/${TAG}_ncu_energy.log 2>&1
-      echo "[$st] rc=$? $(tail -2 $O/${TAG}_ncu_energy.log | tr '\n' ' ')";;
+      for K in k_energy k_knn_distance; do
+        timeout 900 ncu --set full --clock-control none --import-source on -k regex:"${K}\$" -c 1 -f -o $O/${TAG}_$K \
+          python /tmp/ncu_energy.py > $O/${TAG}_ncu_$K.log 2>&1
+        echo "[$st] $K rc=$? $(tail -2 $O/${TAG}_ncu_$K.log | tr '\n' ' ')"
+      done;;
     lab)
       # lab[:nacts]: every library build under gravidy_b200/lab/ against the production library: forces bit for bit
       # (tools/lab/force_cmp.sh) and the big-block rates (tools/sweep_big.py)
