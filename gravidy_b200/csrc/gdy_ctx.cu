@@ -20,6 +20,9 @@
 #include <cstdlib>
 #include <cstring>
 #include <dlfcn.h>
+#include <future>
+#include <memory>
+#include <thread>
 #include <unistd.h>
 #include <nccl.h>   // types only; the library is bound with dlopen so that a process which already
                     // carries an NCCL (e.g. torch's bundled one) shares it instead of loading a second.
@@ -367,8 +370,28 @@ extern "C" int gdy_create_sharded(gdy_ctx **out, uint32_t n, double e2, float et
             if (!nccl_load()) { rc = fail(c, GDY_ERR_NCCL, "libnccl.so.2 not loadable: %s", dlerror()); break; }
             ncclUniqueId id;
             memcpy(&id, nccl_uid, sizeof id);
-            ncclResult_t r = g_nccl.CommInitRank(&c->comm, world, id, rank);
-            if (r != ncclSuccess) { rc = fail(c, GDY_ERR_NCCL, "ncclCommInitRank: %s", g_nccl.GetErrorString(r)); break; }
+            // ncclCommInitRank blocks until all `world` ranks have called it: a rank that never comes would hang this
+            // one for ever.  The call runs on a helper thread and this one waits GDY_NCCL_INIT_TIMEOUT_MS (default
+            // 120 000) for it; on expiry the context is refused with an error (the reference's convention is report +
+            // exit: src/include/gpu/Hermite4GPU.cuh:43-50) and the helper, which cannot be cancelled, is left behind.
+            struct InitJob { ncclComm_t comm = nullptr; ncclResult_t res = ncclSuccess; std::promise<void> done; };
+            std::shared_ptr<InitJob> job = std::make_shared<InitJob>();
+            std::future<void> fut = job->done.get_future();
+            std::thread([job, id, world, rank, device]() {
+                cudaSetDevice(device);
+                job->res = g_nccl.CommInitRank(&job->comm, world, id, rank);
+                job->done.set_value();
+            }).detach();
+            long tmo = 120000;
+            if (const char *e = getenv("GDY_NCCL_INIT_TIMEOUT_MS")) { const long v = atol(e); if (v > 0) tmo = v; }
+            if (fut.wait_for(std::chrono::milliseconds(tmo)) != std::future_status::ready)
+            {
+                rc = fail(c, GDY_ERR_NCCL, "ncclCommInitRank: rank %d of %d waited %ld ms for the other ranks (a rank is missing or "
+                          "holds a different unique id)", rank, world, tmo);
+                break;
+            }
+            if (job->res != ncclSuccess) { rc = fail(c, GDY_ERR_NCCL, "ncclCommInitRank: %s", g_nccl.GetErrorString(job->res)); break; }
+            c->comm = job->comm;
         }
     } while (0);
     if (rc)
@@ -908,7 +931,7 @@ extern "C" int gdy_find_particles_to_move(gdy_ctx *c, double itime, uint32_t *na
     BIND(c);
     int r;
     if ((r = launch_sched(c, itime, false))) return r;
-    CU(cudaStreamSynchronize(c->st));
+    if ((r = wait_sched(c))) return r;
     if ((r = check_abort(c))) return r;
     c->last_nact = c->pin->sched.nact;
     if (nact_out) *nact_out = c->last_nact;

@@ -62,7 +62,10 @@ int gdy_create(gdy_ctx **out, uint32_t n, double e2, float eta, int device);
  * reference partition: src/include/gpu/Hermite4GPU.cu:81-97).  State is replicated; partial forces
  * are summed with ncclAllReduce (replaces the host-side sum, reference: Hermite4GPU.cu:512-530).
  * nccl_uid: GDY_NCCL_UID_BYTES bytes from gdy_nccl_unique_id() on rank 0, distributed by the
- * caller (MPI, torch.distributed, a file, ...).  world == 1 ignores it (may be NULL). */
+ * caller (MPI, torch.distributed, a file, ...).  world == 1 ignores it (may be NULL).
+ * Collective: returns when all `world` ranks have called it; a rank that waits longer than
+ * GDY_NCCL_INIT_TIMEOUT_MS (environment, default 120000) for the others gets GDY_ERR_NCCL instead of
+ * hanging (the reference reports and exits: src/include/gpu/Hermite4GPU.cuh:43-50). */
 int gdy_create_sharded(gdy_ctx **out, uint32_t n, double e2, float eta, int device, int rank,
                        int world, const uint8_t *nccl_uid);
 /* world > 1 with nccl_uid == NULL makes a LOGICAL shard: no communicator, force results are this

@@ -223,3 +223,32 @@ def test_missing_peer_is_an_error_not_a_hang(H, monkeypatch):
     assert time.perf_counter() - t0 < 60
     assert err[1] is None and isinstance(err[0], capi.GdyError), err
     assert "watchdog" in str(err[0])
+
+
+def test_missing_rank_at_create_is_an_error_not_a_hang():
+    """Rank 0 of a world of two creates its context, rank 1 never does: ncclCommInitRank would block for ever;
+    gdy_create_sharded gives up after GDY_NCCL_INIT_TIMEOUT_MS with GDY_ERR_NCCL.  In a process of its own: the helper
+    thread that is left inside NCCL must not outlive anything but that process."""
+    import os
+    import subprocess
+    import sys
+    code = (
+        "import os, sys, time\n"
+        "sys.path.insert(0, %r)\n"
+        "os.environ['GDY_NCCL_INIT_TIMEOUT_MS'] = '3000'\n"
+        "import numpy as np\n"
+        "from gravidy_b200 import capi\n"
+        "from gravidy_b200.hermite4 import Hermite4B200\n"
+        "from gravidy_b200.plummer import plummer\n"
+        "m, r, v = plummer(512, seed=1)\n"
+        "uid = Hermite4B200.nccl_unique_id()\n"
+        "t0 = time.perf_counter()\n"
+        "try:\n"
+        "    Hermite4B200(m, r, v, device=0, rank=0, world=2, nccl_uid=uid)\n"
+        "    print('CREATED')\n"
+        "except capi.GdyError as e:\n"
+        "    print('ERROR after %%.1f s: %%s' %% (time.perf_counter() - t0, e))\n"
+        "sys.stdout.flush()\n"
+        "os._exit(0)\n" % os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    p = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=120)
+    assert "ERROR after" in p.stdout and "waited 3000 ms for the other ranks" in p.stdout, (p.stdout, p.stderr[-2000:])
