@@ -3,6 +3,7 @@
 # Every stage writes gpurun_out/<TAG>_<stage>.{log,json,...}; a stage is `name` or `name:arg1:arg2`.
 #
 #   tests            pytest -m gpu (whole suite)                 tests:<file-or-k-expr>  a subset
+#   smoke            __graft_entry__.build() + smoke()
 #   bench[:N]        bench.py on N GPUs (default 1)               benchref  bench.py --impl reference
 #   lat:<n>[:spec]   tools/step_latency.py at n particles         integ:<n>:<tend>[:gpus[:extra env]]  tools/integrate.py
 #   ncu_force        ncu --set full of the force kernel in bench.py (one capture) + launch list
@@ -30,6 +31,9 @@ for st in "$@"; do
       if [ "$g" = 1 ]; then timeout 1500 python bench.py ${a2:-} > $O/${TAG}_bench_1gpu.json 2> $O/${TAG}_bench_1gpu.err
       else timeout 1500 bash -c "$(declare -f TR); TR $g bench.py --gpus $g ${a2:-}" > $O/${TAG}_bench_${g}gpu.json 2> $O/${TAG}_bench_${g}gpu.err; fi
       echo "[$st] rc=$? $(tail -c 600 $O/${TAG}_bench_${g}gpu.json)";;
+    smoke)
+      timeout 600 python __graft_entry__.py --smoke > $O/${TAG}_smoke.log 2>&1
+      echo "[$st] rc=$? $(tail -1 $O/${TAG}_smoke.log)";;
     benchref)
       timeout 900 python bench.py --impl reference > $O/${TAG}_bench_reference.json 2> $O/${TAG}_bench_reference.err
       echo "[$st] rc=$? $(tail -c 300 $O/${TAG}_bench_reference.json)";;
