@@ -40,7 +40,7 @@ sys.path.insert(0, ROOT)
 FLOP_PER_PAIR = 60.0
 METRIC = "hermite_fp64_gflops_60flop_per_pair_N256k"
 UNIT = "GFLOP/s"
-NCU_DRAM_BYTES_PER_LAUNCH = 14928384 + 3308544   # profiles/r02_force_warp_ncu.md
+NCU_DRAM_BYTES_PER_LAUNCH = 14886912 + 2654720   # profiles/r02_force_warp_ncu.md (capture r02u)
 
 
 def parse_args():
@@ -551,7 +551,7 @@ def run_b200(args, m, r, v):
                          "traffic": NCU_DRAM_BYTES_PER_LAUNCH if (n == 262144 and world == 1) else None,
                          "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of one ncu --set full "
                                            "capture of this kernel at N=262144 on 1 GPU "
-                                           "(profiles/r02_force_warp_ncu.md): 14.93 MB + 3.31 MB; "
+                                           "(profiles/r02_force_warp_ncu.md): 14.89 MB + 2.65 MB; "
                                            "algorithmic 14.7 MB in + 12.6 MB out",
                          "kernel": "k_force_warp<IPT=2,WI=1,WJ=4,NST=3> (warp_i64, 24 waves of CTAs)",
                          "peak_source": "DFMA micro-benchmark on this GPU (gdy_measure_fp64_peak); "
