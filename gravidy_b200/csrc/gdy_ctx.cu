@@ -12,6 +12,7 @@
 #include "gdy_persist.cuh"
 #include "gdy_persist2.cuh"
 
+#include <algorithm>
 #include <atomic>
 #include <chrono>
 #include <cmath>
@@ -88,6 +89,7 @@ struct gdy_ctx
     size_t pool_doubles = 0;
     State s{};
     uint32_t *d_move = nullptr;      // s.move
+    uint32_t *d_move_alt = nullptr;  // the list gdy_next_integration_time prepares for the next find_particles_to_move
     uint32_t *d_ilist = nullptr;     // explicit list for gdy_force_sweep
     uint32_t *d_block_cnt = nullptr;
     uint32_t n_sched_blocks = 0;
@@ -99,7 +101,7 @@ struct gdy_ctx
     double *d_stage = nullptr;       // AoS staging, npad*8 doubles
     size_t part_cap = 0;             // doubles in s.part
 
-    struct Pinned { SchedOut sched; double atime; double energy[2]; uint32_t abort; } *pin = nullptr;
+    struct Pinned { SchedOut sched; double atime; double energy[2]; uint32_t abort; uint32_t atime_seq; } *pin = nullptr;
 
     uint32_t blk_begin = 0, blk_end = 0;     // this shard's j-blocks (units of JB = 64 particles)
     int num_sms = 148;
@@ -108,6 +110,9 @@ struct gdy_ctx
     int tune_variant = -1, tune_jsplit = -1;
     uint32_t seq = 0;
     uint32_t last_nact = 0;
+    // hook loop: next_integration_time already ran the scheduler for the time it returned (one wait per block step)
+    bool sched_cached = false;
+    double sched_cached_time = 0.0;
     bool have_particles = false, have_pred = false;
     uint64_t launches = 0;
     double force_ms_acc = 0.0;
@@ -262,6 +267,8 @@ int alloc_all(gdy_ctx *c)
 
     CU(cudaMalloc(&c->d_move, np * sizeof(uint32_t)));
     CU(cudaMemsetAsync(c->d_move, 0xFF, np * sizeof(uint32_t), c->st));
+    CU(cudaMalloc(&c->d_move_alt, np * sizeof(uint32_t)));
+    CU(cudaMemsetAsync(c->d_move_alt, 0xFF, np * sizeof(uint32_t), c->st));
     s.move = c->d_move;
     CU(cudaMalloc(&c->d_ilist, np * sizeof(uint32_t)));
     CU(cudaMalloc(&c->d_counter, np * sizeof(uint32_t)));
@@ -428,7 +435,7 @@ extern "C" int gdy_destroy(gdy_ctx *c)
     cudaSetDevice(c->device);
     if (c->st) cudaStreamSynchronize(c->st);
     if (c->comm && g_nccl.ok) g_nccl.CommDestroy(c->comm);
-    cudaFree(c->pool); cudaFree(c->d_move); cudaFree(c->d_ilist); cudaFree(c->d_block_cnt);
+    cudaFree(c->pool); cudaFree(c->d_move); cudaFree(c->d_move_alt); cudaFree(c->d_ilist); cudaFree(c->d_block_cnt);
     cudaFree(c->d_block_min); cudaFree(c->d_sched); cudaFree(c->d_atime); cudaFree(c->d_energy);
     cudaFree(c->d_stage); cudaFree(c->d_counter);
     cudaFree(c->ps_ctl);
@@ -480,6 +487,7 @@ extern "C" int gdy_upload_particles(gdy_ctx *c, const double *r4, const double *
     if (!c) return GDY_ERR_INVALID;
     if (!r4 || !v4) return fail(c, GDY_ERR_INVALID, "r4/v4 is NULL");
     BIND(c);
+    c->sched_cached = false;
     State &s = c->s;
     Cols rc{}, vc{};
     rc.c[0] = s.x; rc.c[1] = s.y; rc.c[2] = s.z; rc.c[3] = s.m;
@@ -524,6 +532,7 @@ extern "C" int gdy_upload_times(gdy_ctx *c, const double *t, const double *dt)
     if (!c) return GDY_ERR_INVALID;
     if (!t || !dt) return fail(c, GDY_ERR_INVALID, "t/dt is NULL");
     BIND(c);
+    c->sched_cached = false;
     CU(cudaMemcpyAsync(c->s.t, t, (size_t)c->n * sizeof(double), cudaMemcpyHostToDevice, c->st));
     CU(cudaMemcpyAsync(c->s.dt, dt, (size_t)c->n * sizeof(double), cudaMemcpyHostToDevice, c->st));
     CU(cudaStreamSynchronize(c->st));
@@ -835,6 +844,7 @@ extern "C" int gdy_init_dt(gdy_ctx *c, float eta_s, double itime, double *atime_
 {
     if (!c) return GDY_ERR_INVALID;
     BIND(c);
+    c->sched_cached = false;
     // Host arithmetic with libm log/pow/ceil exactly as the reference does it (src/include/Hermite4.cpp:
     // 108-140): a device log could round differently and flip a timestep level.
     std::vector<double> f((size_t)c->n * 6), t(c->n), dt(c->n);
@@ -865,9 +875,10 @@ namespace {
 
 // find_particles_to_move on the device.  from_min: ITIME = the minimum left in d_block_min by
 // k_min_time (chained scheduler), else the `itime` argument.  Leaves {itime, nact} in the pinned slot.
-int launch_sched(gdy_ctx *c, double itime, bool from_min)
+int launch_sched(gdy_ctx *c, double itime, bool from_min, uint32_t *list_out = nullptr)
 {
-    State &s = c->s;
+    State s = c->s;
+    if (list_out) s.move = list_out;   // the hook loop's look-ahead: State.move keeps the current step's list
     const double *bm = from_min ? c->d_block_min : nullptr;
     ++c->seq;
     k_sched_count<<<c->n_sched_blocks, SCHED_BLOCK, 0, c->st>>>(s, c->n, itime, bm, c->n_min_blocks, c->d_block_cnt);
@@ -933,9 +944,20 @@ extern "C" int gdy_find_particles_to_move(gdy_ctx *c, double itime, uint32_t *na
     if (!c) return GDY_ERR_INVALID;
     BIND(c);
     int r;
-    if ((r = launch_sched(c, itime, false))) return r;
-    if ((r = wait_sched(c))) return r;
-    if ((r = check_abort(c))) return r;
+    if (c->sched_cached && itime == c->sched_cached_time)
+    {
+        // gdy_next_integration_time left the list (in the alternate buffer) and the count for exactly this time
+        c->sched_cached = false;
+        std::swap(c->d_move, c->d_move_alt);
+        c->s.move = c->d_move;
+    }
+    else
+    {
+        c->sched_cached = false;
+        if ((r = launch_sched(c, itime, false))) return r;
+        if ((r = wait_sched(c))) return r;
+        if ((r = check_abort(c))) return r;
+    }
     c->last_nact = c->pin->sched.nact;
     if (nact_out) *nact_out = c->last_nact;
     return GDY_OK;
@@ -1005,6 +1027,7 @@ extern "C" int gdy_correction_pos_vel(gdy_ctx *c, double itime, uint32_t nact)
     if (!c) return GDY_ERR_INVALID;
     if (nact > c->n) return fail(c, GDY_ERR_INVALID, "nact %u > n %u", nact, c->n);
     BIND(c);
+    c->sched_cached = false;
     if (nact == 0) return GDY_OK;
     k_correct<<<cdiv(nact, 128), 128, 0, c->st>>>(c->s, nact, itime, (double)c->eta, nullptr, 0, XRecv{});
     LAUNCHED(c);
@@ -1016,11 +1039,16 @@ extern "C" int gdy_next_integration_time(gdy_ctx *c, double *atime_out)
     if (!c) return GDY_ERR_INVALID;
     BIND(c);
     int r;
+    // The scheduler of the NEXT block step is chained behind the minimum (as in gdy_run): the loop's next call is
+    // find_particles_to_move(ATIME) with the time returned here, which then has its answer already — one host wait per
+    // block step of the hook loop instead of two.  Any call that changes t or dt in between drops the cached answer.
     if ((r = launch_min_time(c))) return r;
-    k_min_final<<<1, 256, 0, c->st>>>(c->d_block_min, c->n_min_blocks, c->d_atime, &c->pin->atime);
-    LAUNCHED(c);
-    CU(cudaStreamSynchronize(c->st));
-    if (atime_out) *atime_out = c->pin->atime;
+    if ((r = launch_sched(c, 0.0, true, c->d_move_alt))) return r;
+    if ((r = wait_sched(c))) return r;
+    if ((r = check_abort(c))) return r;
+    c->sched_cached = true;
+    c->sched_cached_time = c->pin->sched.itime;
+    if (atime_out) *atime_out = c->pin->sched.itime;
     return GDY_OK;
 }
 
@@ -1369,6 +1397,7 @@ extern "C" int gdy_run(gdy_ctx *c, double atime, double itime0, double t_stop, u
 {
     if (!c) return GDY_ERR_INVALID;
     BIND(c);
+    c->sched_cached = false;
     int r;
     if ((r = need_particles(c))) return r;
     State &s = c->s;
@@ -1450,7 +1479,8 @@ extern "C" int gdy_run(gdy_ctx *c, double atime, double itime0, double t_stop, u
         if ((r = launch_min_time(c))) return r;
         if (last)
         {
-            k_min_final<<<1, 256, 0, c->st>>>(c->d_block_min, c->n_min_blocks, c->d_atime, &c->pin->atime);
+            ++c->seq;
+            k_min_final<<<1, 256, 0, c->st>>>(c->d_block_min, c->n_min_blocks, c->d_atime, &c->pin->atime, &c->pin->atime_seq, c->seq);
             LAUNCHED(c);
         }
         else if ((r = launch_sched(c, 0.0, true))) return r;
@@ -1512,6 +1542,7 @@ extern "C" int gdy_force_sweep(gdy_ctx *c, uint32_t nact, const uint32_t *move, 
     if (!c) return GDY_ERR_INVALID;
     if (nact == 0 || nact > c->n || !move) return fail(c, GDY_ERR_INVALID, "bad active list (nact %u, n %u)", nact, c->n);
     BIND(c);
+    c->sched_cached = false;
     if (!c->have_pred) return fail(c, GDY_ERR_STATE, "force_sweep before predicted_pos_vel/init_acc_jrk");
     for (uint32_t k = 0; k < nact; ++k)
         if (move[k] >= c->n) return fail(c, GDY_ERR_INVALID, "move[%u] = %u out of range", k, move[k]);
@@ -1537,6 +1568,7 @@ extern "C" int gdy_force_sweep_full(gdy_ctx *c, int reps, float *ms_out)
     if (!c) return GDY_ERR_INVALID;
     if (reps < 1) return fail(c, GDY_ERR_INVALID, "reps must be >= 1");
     BIND(c);
+    c->sched_cached = false;
     if (!c->have_pred) return fail(c, GDY_ERR_STATE, "force_sweep_full before predicted_pos_vel/init_acc_jrk");
     // the context's own event pair (force_eval leaves it alone when it is not asked to time): nothing to leak on an
     // error return

@@ -403,14 +403,20 @@ __device__ __forceinline__ double fold_block_min(const double *__restrict__ bloc
 }
 
 __global__ void __launch_bounds__(256)
-k_min_final(const double *__restrict__ block_min, uint32_t nmin, double *atime_dev, double *atime_host)
+k_min_final(const double *__restrict__ block_min, uint32_t nmin, double *atime_dev, volatile double *atime_host,
+            volatile uint32_t *seq_host, uint32_t seq)
 {
     __shared__ double sm[8];
     const double m = fold_block_min(block_min, nmin, sm);
     if (threadIdx.x == 0)
     {
         *atime_dev = m;
-        if (atime_host) *atime_host = m;
+        if (atime_host)
+        {
+            *atime_host = m;
+            __threadfence_system();
+            *seq_host = seq;   // written last: the host polls on it
+        }
     }
 }
 

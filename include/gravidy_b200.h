@@ -109,7 +109,10 @@ int gdy_init_acc_jrk(gdy_ctx *ctx);
 int gdy_init_dt(gdy_ctx *ctx, float eta_s, double itime, double *atime_out);
 
 /* find_particles_to_move(ITIME): device compaction in ascending index order
- * (reference: src/include/Hermite4.cpp:63-84). */
+ * (reference: src/include/Hermite4.cpp:63-84).  When ITIME is the time the preceding gdy_next_integration_time
+ * returned and no call changed t or dt in between (the reference's loop), the answer is already there: that call ran
+ * the scheduler for its result into a second list buffer, and this one only swaps the buffers — one host wait per
+ * block step of the hook loop instead of two (11 us per block step, profiles/r02_hook_loop.md). */
 int gdy_find_particles_to_move(gdy_ctx *ctx, double itime, uint32_t *nact_out);
 
 /* save_old_acc_jrk(nact) (reference: src/include/Hermite4.cpp:145-153). */
@@ -129,7 +132,8 @@ int gdy_update_acc_jrk(gdy_ctx *ctx, uint32_t nact);
  * src/include/cpu/Hermite4CPU.cpp:370-411, src/include/utils/NbodyUtils.cpp:337-424). */
 int gdy_correction_pos_vel(gdy_ctx *ctx, double itime, uint32_t nact);
 
-/* next_integration_time(ATIME) (reference: src/include/Hermite4.cpp:90-102). */
+/* next_integration_time(ATIME) (reference: src/include/Hermite4.cpp:90-102).  The active list of the current step
+ * (the `move` array of gdy_download_state) stays as the last gdy_find_particles_to_move left it. */
 int gdy_next_integration_time(gdy_ctx *ctx, double *atime_out);
 
 /* get_energy_gpu() + k_energy (reference: Hermite4GPU.cu:540-592, Hermite4GPU_kernels.cu:250-288;

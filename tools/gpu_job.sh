@@ -3,6 +3,7 @@
 # Every stage writes gpurun_out/<TAG>_<stage>.{log,json,...}; a stage is `name` or `name:arg1:arg2`.
 #
 #   tests            pytest -m gpu (whole suite)                 tests:<file-or-k-expr>  a subset
+#   hooks[:n]        tools/hook_latency.py: the hook loop beside gdy_run, production and lab builds
 #   smoke            __graft_entry__.build() + smoke()
 #   bench[:N]        bench.py on N GPUs (default 1)               benchref  bench.py --impl reference
 #   lat:<n>[:spec]   tools/step_latency.py at n particles         integ:<n>:<tend>[:gpus[:extra env]]  tools/integrate.py
@@ -34,6 +35,11 @@ for st in "$@"; do
     smoke)
       timeout 600 python __graft_entry__.py --smoke > $O/${TAG}_smoke.log 2>&1
       echo "[$st] rc=$? $(tail -1 $O/${TAG}_smoke.log)";;
+    hooks)
+      # hooks[:n]: the hook loop's per-step time, production library and every build under gravidy_b200/lab/
+      timeout 300 python tools/hook_latency.py --n ${a1:-262144} > $O/${TAG}_hooks.txt 2>&1
+      for L in gravidy_b200/lab/*.so; do [ -f "$L" ] && GDY_LIB=$PWD/$L timeout 300 python tools/hook_latency.py --n ${a1:-262144} >> $O/${TAG}_hooks.txt 2>&1; done
+      cat $O/${TAG}_hooks.txt;;
     benchref)
       timeout 900 python bench.py --impl reference > $O/${TAG}_bench_reference.json 2> $O/${TAG}_bench_reference.err
       echo "[$st] rc=$? $(tail -c 300 $O/${TAG}_bench_reference.json)";;
