@@ -1,7 +1,7 @@
 // gdy_persist2.cuh — the persistent small-step kernel, second design: state-resident, no grid barrier.
 //
-// Same job as k_persist_steps (gdy_persist.cuh): the reference loop body (reference:
-// src/include/cpu/Hermite4CPU_integration.cpp:81-124) for runs of block steps with small active sets, one
+// Same job as round 1's k_persist_steps (removed; its building blocks live on in gdy_persist.cuh): the reference loop
+// body (reference: src/include/cpu/Hermite4CPU_integration.cpp:81-124) for runs of block steps with small active sets, one
 // cooperative launch, one CTA per SM.  What the first design paid per step — two grid barriers and a pass over
 // the raw state of all N particles in L2 — is gone:
 //

@@ -4,6 +4,7 @@
 #
 #   tests            pytest -m gpu (whole suite)                 tests:<file-or-k-expr>  a subset
 #   hooks[:n]        tools/hook_latency.py: the hook loop beside gdy_run, production and lab builds
+#   configs          BASELINE configs 2 and 3 to t = 1 on one GPU + the sweep at N = 64k, 128k, 512k
 #   smoke            __graft_entry__.build() + smoke()
 #   bench[:N]        bench.py on N GPUs (default 1)               benchref  bench.py --impl reference
 #   lat:<n>[:spec]   tools/step_latency.py at n particles         integ:<n>:<tend>[:gpus[:extra env]]  tools/integrate.py
@@ -40,6 +41,21 @@ for st in "$@"; do
       timeout 300 python tools/hook_latency.py --n ${a1:-262144} > $O/${TAG}_hooks.txt 2>&1
       for L in gravidy_b200/lab/*.so; do [ -f "$L" ] && GDY_LIB=$PWD/$L timeout 300 python tools/hook_latency.py --n ${a1:-262144} >> $O/${TAG}_hooks.txt 2>&1; done
       cat $O/${TAG}_hooks.txt;;
+    configs)
+      # BASELINE.json configs 2, 3 (N = 16k equal mass, N = 64k Salpeter, to t = 1) and the other sizes of config 5's sweep
+      timeout 300 python tools/integrate.py --particles 16384 --tend 1 > $O/${TAG}_integ_n16k.json 2> $O/${TAG}_integ_n16k.err
+      timeout 300 python tools/integrate.py --particles 65536 --tend 1 --spectrum salpeter > $O/${TAG}_integ_n64k_salpeter.json 2> $O/${TAG}_integ_n64k_salpeter.err
+      for n in 65536 131072 524288; do timeout 300 python tools/sweep_big.py --n $n --nacts $n --variants 2 --reps 3; done > $O/${TAG}_sweep_sizes.txt 2>&1
+      python - <<PY
+import json
+for f in ("$O/${TAG}_integ_n16k.json", "$O/${TAG}_integ_n64k_salpeter.json"):
+    try:
+        d = json.loads(open(f).read().strip().splitlines()[-1])
+        print(f, "wall", round(d["wall_s"], 3), "steps", d["block_steps"], "E", d["cum_rel_energy_error"], "persist", d["persist_steps"], "gflops", round(d.get("gflops", 0)))
+    except Exception as e:
+        print(f, "no result:", e)
+PY
+      grep -E "^[0-9]+,[0-9]+,-1" $O/${TAG}_sweep_sizes.txt;;
     benchref)
       timeout 900 python bench.py --impl reference > $O/${TAG}_bench_reference.json 2> $O/${TAG}_bench_reference.err
       echo "[$st] rc=$? $(tail -c 300 $O/${TAG}_bench_reference.json)";;
