@@ -5,6 +5,7 @@
 #   tests            pytest -m gpu (whole suite)                 tests:<file-or-k-expr>  a subset
 #   hooks[:n]        tools/hook_latency.py: the hook loop beside gdy_run, production and lab builds
 #   configs          BASELINE configs 2 and 3 to t = 1 on one GPU + the sweep at N = 64k, 128k, 512k
+#   p2prof[:n:steps] phase profile of the persistent kernel by active-set size on a small model (cap 2048)
 #   smoke            __graft_entry__.build() + smoke()
 #   bench[:N]        bench.py on N GPUs (default 1)               benchref  bench.py --impl reference
 #   lat:<n>[:spec]   tools/step_latency.py at n particles         integ:<n>:<tend>[:gpus[:extra env]]  tools/integrate.py
@@ -56,6 +57,17 @@ for f in ("$O/${TAG}_integ_n16k.json", "$O/${TAG}_integ_n64k_salpeter.json"):
         print(f, "no result:", e)
 PY
       grep -E "^[0-9]+,[0-9]+,-1" $O/${TAG}_sweep_sizes.txt;;
+    p2prof)
+      # p2prof:<n>:<steps>: the persistent kernel with the cap at 2048 on a small model (N = 32768 on one GPU gives every CTA the
+      # 222-particle slice of an N = 256k run on eight): per-step medians by nact bin, then the phase profile of CTA 0
+      # restricted to block steps of at most 64 ... 2048 active particles (differences = cost of the extra i-chunks)
+      n=${a1:-32768}; k=${a2:-6000}
+      GDY_PERSIST_NACT=2048 timeout 300 python tools/step_latency.py --n $n --steps $k > $O/${TAG}_p2prof.txt 2>&1
+      for f in 16 64 128 256 512 1024 2048; do
+        echo "== phases of the block steps with nact <= $f" >> $O/${TAG}_p2prof.txt
+        GDY_PERSIST_NACT=2048 GDY_PERSIST_PROF=1 GDY_PERSIST_PROF_NACT=$f timeout 300 python tools/step_latency.py --n $n --steps $k 2>&1 | grep -E "ns/step|persistent kernel" >> $O/${TAG}_p2prof.txt
+      done
+      cat $O/${TAG}_p2prof.txt;;
     benchref)
       timeout 900 python bench.py --impl reference > $O/${TAG}_bench_reference.json 2> $O/${TAG}_bench_reference.err
       echo "[$st] rc=$? $(tail -c 300 $O/${TAG}_bench_reference.json)";;

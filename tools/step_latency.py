@@ -32,7 +32,9 @@ print(f"  persistent kernel: {pl} launches, {ps} block steps ({ps / max(pl, 1):.
 if any(prof) and os.environ.get("GDY_PERSIST_V", "2") != "1":
     names = ["load", "A.publish", "B.predict+scan", "P1.wait_i", "P1.pairs+publish", "P2", "P3.wait", "P3.lists", "exit",
              "-", "-", "-", "xchg.wait_total", "xchg.count", "-", "-"]
-    print("  ns/step by phase (CTA 0, v2): " + "  ".join(f"{nm} {v / max(ps, 1):.0f}" for nm, v in zip(names, prof) if v))
+    cnt = prof[14] or ps   # block steps the timers ran on (GDY_PERSIST_PROF_NACT restricts them by active-set size)
+    print(f"  ns/step by phase (CTA 0, v2, {cnt} profiled block steps): " + "  ".join(
+        f"{nm} {v / max(cnt, 1):.0f}" for nm, v in zip(names, prof) if v and nm != "-" and nm != "xchg.count"))
 elif any(prof):
     names = ["P1a", "P1b", "bar1", "P2", "bar2", "P3", "exit", "-", "b.stage", "b.sync", "b.pairs", "b.foldsync", "-", "-", "-", "-"]
     print("  ns/step by phase (CTA 0): " + "  ".join(f"{nm} {v / max(ps, 1):.0f}" for nm, v in zip(names, prof) if v))
