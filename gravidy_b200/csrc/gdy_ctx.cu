@@ -898,6 +898,9 @@ int wait_pinned(gdy_ctx *c, const volatile uint32_t *word, uint32_t want, const 
 {
     for (uint32_t spin = 0; *word != want; ++spin)
     {
+#if defined(__x86_64__) || defined(__i386__)
+        __builtin_ia32_pause();   // a polite spin: the sibling hyper-thread (another rank's host thread) keeps its share
+#endif
         if ((spin & 255u) == 255u)
         {
             const cudaError_t q = cudaStreamQuery(c->st);
