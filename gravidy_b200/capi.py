@@ -20,6 +20,7 @@ _ctx = C.c_void_p
 GDY_OK, GDY_ERR_INVALID, GDY_ERR_NO_DEVICE, GDY_ERR_CUDA, GDY_ERR_NCCL, GDY_ERR_STATE = 0, -1, -2, -3, -4, -5
 NCCL_UID_BYTES = 128
 PEER_HANDLE_BYTES = 128
+NOALLOC_MAX_N = 1 << 20   # GDY_NOALLOC_MAX_N
 
 
 class RunStats(C.Structure):
@@ -65,6 +66,8 @@ SIGNATURES = {
     "gdy_energy": (C.c_int, [_ctx, _dp, _dp]),
     "gdy_energy_timed": (C.c_int, [_ctx, _dp, _dp, _fp]),
     "gdy_neighbour_timed": (C.c_int, [_ctx, C.c_int, _fp]),
+    # device pointers and a cudaStream_t, all as integers (the caller owns the memory: nothing is allocated)
+    "gdy_energy_noalloc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p]),
     "gdy_run": (C.c_int, [_ctx, C.c_double, C.c_double, C.c_double, C.c_uint64,
                           C.POINTER(RunStats), _up, _dp, _fp, C.c_uint64]),
     "gdy_force_sweep": (C.c_int, [_ctx, C.c_uint32, _up, _dp, _fp]),

@@ -1648,3 +1648,160 @@ extern "C" int gdy_measure_copy_bw(gdy_ctx *c, double *gbs_out)
     if (gbs_out) *gbs_out = 2.0 * bytes / (best * 1e-3) / 1e9;
     return GDY_OK;
 }
+
+#include <mutex>
+
+// ---- total energy for callers that must not allocate ---------------------------------------------------------
+// gdy_energy_noalloc(): the same chunk / j-split / fold decomposition as energy_launch() above, but without a
+// context.  Who needs it: a host program that gave the whole device to its own memory pool at start-up (a
+// cudaMalloc from a library would fail, or eat into a budget the program thinks it owns); an analysis hook that runs
+// between block steps and may not stall the GPU, which cudaMalloc/cudaFree do because they synchronise the device;
+// a plug-in host whose rules forbid driver allocations after initialisation.  Such a caller already holds its
+// particles in device memory; it passes them (and a two-double result slot) in, and the per-CTA partial sums, which
+// gdy_energy keeps in the context's cudaMalloc'ed partial-force buffer, live in the fixed array below instead.
+//
+// g_noalloc_scratch is part of the library image: every GPU that loads libgravidy_b200.so carries these 128 KiB until
+// the process exits, used or not.  All calls on a device share it and it keeps whatever the previous call left.
+// Nothing in it has to start at zero: every slot a call reads (cta_ek[chunk], cta_ep[split][chunk], sums[2][chunk])
+// is written earlier in the same call by exactly one thread, so stale contents are never seen.  Two calls that are in
+// flight on the same GPU at the same time (different streams, or different host threads) write the same slots and race.
+//
+// In host code the identifier g_noalloc_scratch is only a handle for the runtime, not a pointer the GPU can follow,
+// so the host asks for the device address with cudaGetSymbolAddress, once per device and with that device current,
+// and hands that to the kernels.  This happens inside the first call on each device.
+constexpr uint32_t NOALLOC_MAX_N = 1u << 20;          // GDY_NOALLOC_MAX_N in the header
+constexpr size_t NOALLOC_SCRATCH_DOUBLES = 16384;     // need(n) = (nsplit + 3) * ceil(n / 512) <= 8192 for n <= 2^20
+static __device__ __align__(256) double g_noalloc_scratch[NOALLOC_SCRATCH_DOUBLES];
+
+namespace {
+
+// k_energy with the reference's host layout as input: r4 = n x {x, y, z, m}, v4 = n x {vx, vy, vz, _}, no padded
+// copies.  Indices past n are staged as the padding particle of the context path (mass 0 at PAD_POS), masses are
+// narrowed to float like gdy_upload_particles does, and the loop body, tile order and reduction are k_energy's.
+__global__ void __launch_bounds__(EN_T)
+k_energy_aos(const double *__restrict__ r4, const double *__restrict__ v4, uint32_t n, uint32_t tiles_per_split,
+             uint32_t ntiles, double *__restrict__ cta_ek, double *__restrict__ cta_ep, uint32_t nch_total)
+{
+    __shared__ __align__(16) double tile[2][4][EN_TILE];
+    __shared__ double red[8];
+    const int tid = threadIdx.x;
+    const uint32_t chunk = blockIdx.x;
+    const uint32_t i0 = chunk * EN_CHUNK + tid, i1 = i0 + EN_T;
+    const uint32_t c0 = i0 < n ? i0 : n - 1, c1 = i1 < n ? i1 : n - 1;
+    const double x0 = r4[4 * (size_t)c0], y0 = r4[4 * (size_t)c0 + 1], z0 = r4[4 * (size_t)c0 + 2];
+    const double x1 = r4[4 * (size_t)c1], y1 = r4[4 * (size_t)c1 + 1], z1 = r4[4 * (size_t)c1 + 2];
+    const uint32_t t0 = blockIdx.y * tiles_per_split, t1 = min(t0 + tiles_per_split, ntiles);
+    double p0 = 0.0, p1 = 0.0;
+    auto stage = [&](uint32_t t, int b) {
+        const uint32_t j = t * EN_TILE + tid;
+        const bool real = j < n;
+        const double *q = r4 + 4 * (size_t)(real ? j : 0);
+        tile[b][0][tid] = real ? q[0] : PAD_POS;
+        tile[b][1][tid] = real ? q[1] : PAD_POS;
+        tile[b][2][tid] = real ? q[2] : PAD_POS;
+        tile[b][3][tid] = real ? (double)(float)q[3] : 0.0;
+    };
+    if (t0 < t1) stage(t0, 0);
+    __syncthreads();
+    for (uint32_t t = t0; t < t1; ++t)
+    {
+        const int b = (t - t0) & 1;
+        if (t + 1 < t1) stage(t + 1, b ^ 1);
+#pragma unroll 4
+        for (int j = 0; j < EN_TILE; j += 2)
+        {
+            const double2 X = *reinterpret_cast<const double2 *>(&tile[b][0][j]);
+            const double2 Y = *reinterpret_cast<const double2 *>(&tile[b][1][j]);
+            const double2 Z = *reinterpret_cast<const double2 *>(&tile[b][2][j]);
+            const double2 M = *reinterpret_cast<const double2 *>(&tile[b][3][j]);
+#define GDY_EN_PAIR(xi, yi, zi, xj, yj, zj, mj, pot) \
+            { \
+                const double dx = xj - xi, dy = yj - yi, dz = zj - zi; \
+                const double r2 = fma(dz, dz, fma(dy, dy, dx * dx)); \
+                double y = rsqrt_f64(r2); \
+                y = (r2 > 0.0) ? y : 0.0; \
+                pot = fma(mj, y, pot); \
+            }
+            GDY_EN_PAIR(x0, y0, z0, X.x, Y.x, Z.x, M.x, p0)
+            GDY_EN_PAIR(x1, y1, z1, X.x, Y.x, Z.x, M.x, p1)
+            GDY_EN_PAIR(x0, y0, z0, X.y, Y.y, Z.y, M.y, p0)
+            GDY_EN_PAIR(x1, y1, z1, X.y, Y.y, Z.y, M.y, p1)
+#undef GDY_EN_PAIR
+        }
+        __syncthreads();
+    }
+    const double m0 = i0 < n ? (double)(float)r4[4 * (size_t)i0 + 3] : 0.0;
+    const double m1 = i1 < n ? (double)(float)r4[4 * (size_t)i1 + 3] : 0.0;
+    double ep = 0.0, ek = 0.0;
+    if (i0 < n) ep += -0.5 * m0 * p0;
+    if (i1 < n) ep += -0.5 * m1 * p1;
+    ep = block_sum_256(ep, red);
+    if (tid == 0) cta_ep[(size_t)blockIdx.y * nch_total + chunk] = ep;
+    if (blockIdx.y == 0)
+    {
+        if (i0 < n) { const double *w = v4 + 4 * (size_t)i0; const double vx = w[0], vy = w[1], vz = w[2]; ek += 0.5 * m0 * (vx * vx + vy * vy + vz * vz); }
+        if (i1 < n) { const double *w = v4 + 4 * (size_t)i1; const double vx = w[0], vy = w[1], vz = w[2]; ek += 0.5 * m1 * (vx * vx + vy * vy + vz * vz); }
+        ek = block_sum_256(ek, red);
+        if (tid == 0) cta_ek[chunk] = ek;
+    }
+}
+
+// device address of g_noalloc_scratch, looked up once per device (the first call on that device does it)
+constexpr int NOALLOC_MAX_DEVICES = 64;
+std::mutex g_noalloc_mu;
+double *g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {};
+
+int noalloc_scratch(double **out)
+{
+    gdy_ctx *c = nullptr;   // errors go to the slot gdy_last_error(NULL) reads
+    int dev = -1;
+    CU(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= NOALLOC_MAX_DEVICES) return fail(c, GDY_ERR_INVALID, "gdy_energy_noalloc: device ordinal %d out of range", dev);
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    if (!g_noalloc_ptr[dev])
+    {
+        int major = 0;
+        CU(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev));
+        if (major < 10) return fail(c, GDY_ERR_NO_DEVICE, "gdy_energy_noalloc: device %d is not sm_100 (there is no CPU path)", dev);
+        double *p = nullptr;
+        CU(cudaGetSymbolAddress((void **)&p, g_noalloc_scratch));
+        if (!p) return fail(c, GDY_ERR_CUDA, "gdy_energy_noalloc: cudaGetSymbolAddress gave a null address on device %d", dev);
+        g_noalloc_ptr[dev] = p;
+    }
+    *out = g_noalloc_ptr[dev];
+    return 0;
+}
+
+}  // namespace
+
+extern "C" int gdy_energy_noalloc(const double *d_r4, const double *d_v4, uint32_t n, double *d_energy_out, void *stream)
+{
+    gdy_ctx *c = nullptr;
+    if (!d_r4 || !d_v4 || !d_energy_out) return fail(c, GDY_ERR_INVALID, "gdy_energy_noalloc: null device pointer");
+    if (n == 0) return fail(c, GDY_ERR_INVALID, "gdy_energy_noalloc: n = 0");
+    if (n > NOALLOC_MAX_N)
+        return fail(c, GDY_ERR_INVALID, "gdy_energy_noalloc: n = %u is above GDY_NOALLOC_MAX_N = %u, the size the library's fixed "
+                    "scratch array is laid out for; use gdy_energy on a context for larger sets", n, NOALLOC_MAX_N);
+    double *scratch = nullptr;
+    int r;
+    if ((r = noalloc_scratch(&scratch))) return r;
+    cudaStream_t st = (cudaStream_t)stream;
+    // the decomposition of energy_launch() for one GPU: a function of n alone
+    const uint32_t nch_total = cdiv(n, EN_CHUNK), ntiles = round_up(n, PAD) / EN_TILE;
+    uint32_t nsplit = cdiv(8u * 148u, nch_total);
+    if (nsplit > ntiles / 4) nsplit = ntiles / 4 ? ntiles / 4 : 1;
+    if (nsplit < 1) nsplit = 1;
+    const uint32_t per = cdiv(ntiles, nsplit);
+    nsplit = cdiv(ntiles, per);
+    if ((size_t)(nsplit + 3) * nch_total > NOALLOC_SCRATCH_DOUBLES)
+        return fail(c, GDY_ERR_INVALID, "gdy_energy_noalloc: n = %u needs %zu scratch doubles, the fixed array holds %zu",
+                    n, (size_t)(nsplit + 3) * nch_total, NOALLOC_SCRATCH_DOUBLES);
+    double *cta_ek = scratch, *cta_ep = scratch + nch_total, *sums = cta_ep + (size_t)nsplit * nch_total;
+    k_energy_aos<<<dim3(nch_total, nsplit), EN_T, 0, st>>>(d_r4, d_v4, n, per, ntiles, cta_ek, cta_ep, nch_total);
+    CU(cudaGetLastError());
+    k_energy_fold<<<cdiv(nch_total, 256), 256, 0, st>>>(cta_ek, cta_ep, nsplit, nch_total, 0, nch_total, sums);
+    CU(cudaGetLastError());
+    k_sum2<<<1, 1024, 0, st>>>(sums, sums + nch_total, nch_total, d_energy_out);
+    CU(cudaGetLastError());
+    return GDY_OK;
+}

@@ -144,6 +144,34 @@ int gdy_energy(gdy_ctx *ctx, double *ekin_out, double *epot_out);
 /* The same with the pair kernel bracketed by CUDA events (bench: FP64 roofline of k_energy). */
 int gdy_energy_timed(gdy_ctx *ctx, double *ekin_out, double *epot_out, float *ms_out);
 
+/* Total energy WITHOUT a context and without any allocation.  This entry point has no counterpart in the
+ * reference (there get_energy_gpu works on the arrays alloc_arrays_device cudaMalloc'ed); it exists for callers that
+ * cannot let a library allocate device memory: a program that handed the whole GPU to its own memory pool when it
+ * started (a later cudaMalloc fails or breaks its accounting), an analysis hook between block steps that must not stall
+ * the GPU (cudaMalloc and cudaFree synchronise the device), a plug-in host that forbids driver allocations after
+ * start-up.  gdy_create / gdy_energy need cudaMalloc and pinned host memory, so those callers cannot use them.
+ *
+ *   d_r4          DEVICE pointer, n x {x, y, z, m} doubles (the reference's double4 h_r layout); masses are narrowed
+ *                 to float precision like gdy_upload_particles does
+ *   d_v4          DEVICE pointer, n x {vx, vy, vz, _} doubles (double4 h_v)
+ *   n             1 <= n <= GDY_NOALLOC_MAX_N; anything larger is refused with GDY_ERR_INVALID and a message
+ *   d_energy_out  DEVICE pointer, 2 doubles: kinetic, potential (unsoftened), written by the last kernel
+ *   stream        a cudaStream_t (NULL = the default stream).  The call only enqueues three kernels; the result is
+ *                 there once the stream has passed them.  Nothing is copied to the host and nothing is synchronised.
+ * All four pointers belong to the device that is CURRENT on the calling thread.
+ *
+ * The per-CTA partial sums go to a fixed 128 KiB array that is part of the library image: every GPU that loads this
+ * library holds it until the process exits, whether or not this function is ever called, and GDY_NOALLOC_MAX_N is
+ * what fits in it.  The array is shared by all calls on a device and keeps the previous call's contents; nothing in
+ * it needs clearing (every slot a call reads is written earlier in that call), but two calls that overlap on one GPU
+ * (two streams, two threads) overwrite each other's partial sums: serialise them.
+ * The FIRST call on each device looks up the array's device address (and loads the kernels); make that first call
+ * during start-up, before any stream capture begins.  No cudaMalloc / cudaFree / cudaHostAlloc or other allocating
+ * routine is called, on the first call or later.  Same decomposition and summation order as gdy_energy on one GPU.
+ * Errors are reported through gdy_last_error(NULL). */
+#define GDY_NOALLOC_MAX_N 1048576u
+int gdy_energy_noalloc(const double *d_r4, const double *d_v4, uint32_t n, double *d_energy_out, void *stream);
+
 /* Distance of every particle to its k-th nearest neighbour (1 <= k <= 8) at the current positions:
  * the O(N^2) part of NbodyUtils::get_center_of_density (reference: src/include/utils/NbodyUtils.cpp:
  * 163-220, which sorts all N distances per particle on the host and takes d[J], the zero self entry sorted
