@@ -21,7 +21,7 @@
 //     arrays are only ever touched by one CTA of the rank.
 //
 // Ownership makes every raw-state access CTA-local (ordered by __syncthreads), which is what lets the kernel
-// run without a single memory fence.  Every poll is bounded by a %globaltimer watchdog: on expiry the CTA
+// run without a single memory fence.  Every wait is bounded by a %globaltimer watchdog (per wait: cleared on success): on expiry the CTA
 // raises the abort word, every other poll sees it, all CTAs leave, and the host returns GDY_ERR_STATE
 // (the reference's convention is to fail loudly: src/include/gpu/Hermite4GPU.cuh:43-50).
 //
@@ -105,7 +105,10 @@ __host__ __device__ __forceinline__ uint32_t slice_begin(uint32_t len, uint32_t 
     return (uint32_t)(((uint64_t)len * c) / G);
 }
 
+// One wait's watchdog.  t0 = %globaltimer at the first slow look of the CURRENT wait (0 = not yet timed); every wait that
+// succeeds calls watch_reset, so the timeout measures a single wait, never the age of the launch.
 struct Watch { unsigned long long t0; uint32_t spins; };
+__device__ __forceinline__ void watch_reset(Watch &w) { w.t0 = 0ull; w.spins = 0u; }
 
 // true = give up (the watchdog expired here or somewhere else)
 __device__ __forceinline__ bool watch_expired(Watch &w, const Persist2Args &a, uint32_t where)
@@ -130,7 +133,7 @@ __device__ __forceinline__ bool ll_wait(const uint4 *slot, uint32_t tag, double 
     for (;;)
     {
         const uint4 r = ll_load(slot);
-        if (r.y == tag && r.w == tag) { v = ll_value(r); return true; }
+        if (r.y == tag && r.w == tag) { v = ll_value(r); watch_reset(w); return true; }
         if (watch_expired(w, a, where)) { v = 0.0; return false; }
     }
 }
@@ -140,7 +143,7 @@ __device__ __forceinline__ bool ll_wait_sys(const uint4 *slot, uint32_t tag, dou
     for (;;)
     {
         const uint4 r = ll_load_sys(slot);
-        if (r.y == tag && r.w == tag) { v = ll_value(r); return true; }
+        if (r.y == tag && r.w == tag) { v = ll_value(r); watch_reset(w); return true; }
         if (watch_expired(w, a, where)) { v = 0.0; return false; }
     }
 }
@@ -156,7 +159,7 @@ __device__ __forceinline__ bool ll2_wait(const uint2 *slot, uint32_t tag, uint32
     {
         uint2 r;
         asm volatile("ld.relaxed.gpu.global.v2.b32 {%0, %1}, [%2];" : "=r"(r.x), "=r"(r.y) : "l"(slot) : "memory");
-        if (r.y == tag) { v = r.x; return true; }
+        if (r.y == tag) { v = r.x; watch_reset(w); return true; }
         if (watch_expired(w, a, where)) { v = 0u; return false; }
     }
 }
@@ -433,6 +436,7 @@ k_persist2(const Persist2Args a)
                             }
                             if (!ok && watch_expired(wd, a, 2)) { giveup = true; dead = true; }
                         } while (!__all_sync(0xffffffffu, ok || giveup));
+                        if (!giveup) watch_reset(wd);
 #pragma unroll
                         for (int q = 0; q < 5; ++q) if ((uint32_t)(q * 32 + lane) < G) v += ll_value(r[q]);
                     }

@@ -223,8 +223,11 @@ int gdy_set_tuning(gdy_ctx *ctx, int variant, int jsplit);
  * blocks inside gdy_run, without the host (replaces, for those steps, the per-step launch sequence of the reference:
  * src/include/gpu/Hermite4GPU_integration.cpp:81-124).  Every CTA owns a slice of the particles, keeps its raw state
  * resident in shared memory and talks to the other CTAs through flagged slots only: no grid barrier, no fence
- * (csrc/gdy_persist2.cuh).  Every poll in it is bounded by a watchdog (environment GDY_SPIN_TIMEOUT_MS, default 2000):
- * a dead or missing peer makes gdy_run return GDY_ERR_STATE instead of hanging.
+ * (csrc/gdy_persist2.cuh).  Every WAIT in it is bounded by a watchdog (environment GDY_SPIN_TIMEOUT_MS, default 2000,
+ * read at gdy_create): the timer starts when a wait turns slow and is cleared when the wait succeeds, so a launch may
+ * run for any length of time, but a dead or missing peer makes gdy_run return GDY_ERR_STATE instead of hanging.  The
+ * same bound applies to the first exchange after gdy_run is entered: a rank that enters gdy_run more than the timeout
+ * after its peers (e.g. because it alone wrote a snapshot) is taken for dead; drivers with such skew raise the value.
  * nact_max: 0 = off, < 0 = default, at most 2048.  Sharded contexts need gdy_peer_attach first. */
 int gdy_set_persist(gdy_ctx *ctx, int nact_max);
 int gdy_persist_stats(const gdy_ctx *ctx, uint64_t *launches_out, uint64_t *steps_out);

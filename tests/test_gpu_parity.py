@@ -254,6 +254,31 @@ def test_fused_run_equals_hook_loop(H, golden_dir, name, persist):
         np.testing.assert_allclose(a["a2"], b["a2"], rtol=1e-6, atol=1e-6 * np.abs(b["a2"]).max())
 
 
+def test_persistent_launch_may_outlast_the_watchdog(H, monkeypatch):
+    """GDY_SPIN_TIMEOUT_MS bounds ONE wait of the persistent kernel, not the launch: with every block step inside the
+    persistent path (n <= nact_max) a launch runs 4096 steps, far longer than a 20 ms timeout, and must still finish
+    with the schedule of the per-hook kernels (round-2 advisor finding: the timer used to start at a thread's first
+    slow poll and was never reset, so any launch older than the timeout aborted)."""
+    timeout_ms, nsteps = 20, 12000
+    monkeypatch.setenv("GDY_SPIN_TIMEOUT_MS", str(timeout_ms))
+    m, r, v = plummer(1024, seed=default_seed(1024))
+    h = H(m, r, v)
+    h.set_persist(1024)
+    h.init_acc_jrk()
+    atime = h.init_dt(0.0)
+    st, tn, ti = h.run(atime, 1e9, max_steps=nsteps, trace_cap=nsteps)
+    launches, steps = h.persist_stats()
+    assert st.iterations == nsteps and steps == nsteps and 1 <= launches <= 4
+    assert st.wall_ms / launches > timeout_ms, (st.wall_ms, launches)   # the launches did outlast the timeout
+    monkeypatch.delenv("GDY_SPIN_TIMEOUT_MS")
+    h2 = H(m, r, v)
+    h2.set_persist(0)
+    h2.init_acc_jrk()
+    at2 = h2.init_dt(0.0)
+    st2, tn2, ti2 = h2.run(at2, 1e9, max_steps=nsteps, trace_cap=nsteps)
+    assert np.array_equal(tn, tn2) and np.array_equal(ti, ti2) and st.atime == st2.atime
+
+
 # ---- integration to t = 1 (BASELINE configs[0]) ------------------------------------------------------
 def test_run_n1024_to_t1_vs_reference_fixture(H, golden_dir):
     g = _load(golden_dir, "plummer_n1024_t1_eps1e-2")
