@@ -76,6 +76,7 @@ SIGNATURES = {
     "gdy_set_tuning": (C.c_int, [_ctx, C.c_int, C.c_int]),
     "gdy_set_persist": (C.c_int, [_ctx, C.c_int]),
     "gdy_persist_stats": (C.c_int, [_ctx, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
+    "gdy_persist_state": (C.c_int, [_ctx, _up, _up]),
     "gdy_peer_export": (C.c_int, [_ctx, C.POINTER(C.c_uint8)]),
     "gdy_peer_attach": (C.c_int, [_ctx, C.POINTER(C.c_uint8)]),
     "gdy_persist_profile": (C.c_int, [_ctx, C.POINTER(C.c_uint64)]),

@@ -197,7 +197,7 @@ int check_abort(gdy_ctx *c)
 }  // namespace
 
 // ---- lifetime ------------------------------------------------------------------------------------------
-extern "C" int gdy_abi_version(void) { return 2; }
+extern "C" int gdy_abi_version(void) { return 3; }
 
 extern "C" int gdy_device_count(void)
 {
@@ -341,6 +341,9 @@ extern "C" int gdy_create_sharded(gdy_ctx **out, uint32_t n, double e2, float et
     if (!out) return fail(c, GDY_ERR_INVALID, "out is NULL");
     *out = nullptr;
     if (n == 0) return fail(c, GDY_ERR_INVALID, "n must be > 0");
+    // the warp force kernel's pinned instruction groups assume j indices below 2^26 (gdy_force.cuh, `opq`): above
+    // that its never-taken branches WOULD be taken and the forces would be wrong without any error
+    if (n > GDY_MAX_N) return fail(c, GDY_ERR_INVALID, "n = %u is above GDY_MAX_N = %u (the force kernel's index range)", n, (unsigned)GDY_MAX_N);
     if (!(e2 >= 0.0)) return fail(c, GDY_ERR_INVALID, "e2 must be >= 0");
     if (world < 1 || rank < 0 || rank >= world) return fail(c, GDY_ERR_INVALID, "bad rank/world %d/%d", rank, world);
     int ndev = 0;
@@ -1290,6 +1293,27 @@ extern "C" int gdy_set_persist(gdy_ctx *c, int nact_max)
         return fail(c, GDY_ERR_STATE, "a sharded context needs gdy_peer_attach before the persistent path");
     c->ps_nact_max = nact_max < 0 ? PS_DEFAULT_NACT : (uint32_t)nact_max;
     return GDY_OK;
+}
+
+// Whether the persistent path can serve this context, answered without waiting for the first gdy_run (which is where
+// persist2_prepare decides it): the same shared-memory sum as there.
+extern "C" int gdy_persist_state(gdy_ctx *c, uint32_t *smem_need_out, uint32_t *smem_max_out)
+{
+    if (!c) return GDY_ERR_INVALID;
+    BIND(c);
+    const uint32_t G = c->ps_grid ? c->ps_grid : (uint32_t)c->num_sms;
+    uint32_t jb = c->blk_begin * JB, je = c->blk_end * JB < c->n ? c->blk_end * JB : c->n;
+    if (je < jb) je = jb;
+    const uint32_t lf = cdiv(je - jb, G) + 1, ls = cdiv(c->n, G) + 1;
+    int max_optin = 0;
+    CU(cudaDeviceGetAttribute(&max_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, c->device));
+    const size_t off = (sizeof(P2Fixed) + 15) & ~(size_t)15;
+    const size_t need = off + (size_t)7 * round_up(lf, 2) * 8 + (size_t)round_up(ls, 2) * 8;
+    if (smem_need_out) *smem_need_out = (uint32_t)need;
+    if (smem_max_out) *smem_max_out = (uint32_t)max_optin;
+    if (c->ps_nact_max == 0) return 0;
+    if (c->p2_smem == 1 || need > (size_t)max_optin) return 2;
+    return 1;
 }
 
 // ---- peer memory for the fused exchange of the persistent path ------------------------------------------------

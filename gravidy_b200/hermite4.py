@@ -251,6 +251,14 @@ class Hermite4B200:
         self._ck(self.lib.gdy_persist_stats(self.h, C.byref(a), C.byref(b)))
         return a.value, b.value
 
+    def persist_state(self):
+        """(state, smem bytes needed per CTA, device limit): state 0 = off, 1 = available, 2 = the slices do not fit."""
+        need, lim = C.c_uint32(), C.c_uint32()
+        rc = self.lib.gdy_persist_state(self.h, C.byref(need), C.byref(lim))
+        if rc < 0:
+            self._ck(rc)
+        return rc, need.value, lim.value
+
     def persist_profile(self):
         """ns per phase of the persistent kernel (CTA 0); zeros unless GDY_PERSIST_PROF=1."""
         out = (C.c_uint64 * 144)()

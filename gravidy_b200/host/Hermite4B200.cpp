@@ -232,6 +232,13 @@ void Hermite4B200::read_checkpoint(LoopState &ls)
     std::ifstream in(ns->restart_filename.c_str(), std::ios::in | std::ios::binary);
     CkptHeader h;
     in.read(reinterpret_cast<char *>(&h), sizeof(h));
+    if (in.good() && std::memcmp(h.magic, CKPT_MAGIC, 7) == 0 && h.magic[7] != CKPT_MAGIC[7])
+    {
+        // an older (or newer) layout of the same file family: say so instead of "not a checkpoint"
+        logger->log_error(ns->restart_filename + " is a gravidy-b200 checkpoint of format version " + std::string(1, h.magic[7]) +
+                          "; this build reads version " + std::string(1, CKPT_MAGIC[7]) + ": write it again with this build");
+        std::exit(EXIT_FAILURE);
+    }
     if (!in.good() || std::memcmp(h.magic, CKPT_MAGIC, 8) != 0)
     {
         logger->log_error(ns->restart_filename + " is not a gravidy-b200 checkpoint");

@@ -39,8 +39,14 @@ typedef enum gdy_status
 } gdy_status;
 
 #define GDY_NCCL_UID_BYTES 128
+#define GDY_MAX_N 67108863u /* 2^26 - 1 */
 
-/* Version of this ABI (bumped on any signature change). */
+/* Version of this ABI (bumped on any change of a signature or of what an existing call means).
+ *   3: gdy_energy_noalloc added; n limited to GDY_MAX_N; and the number now also covers what changed under version 2
+ *      without a bump: gdy_upload_particles and gdy_energy are COLLECTIVE on sharded contexts that have a communicator
+ *      (every rank must call them; a rank-0-only call blocks in NCCL), masses are stored as (double)(float)m like the
+ *      reference's Predictor.m, and the host program's checkpoint format is GDYCKPT2.
+ *   2: sharded contexts, persistent kernel, peer exchange.   1: round-1 hooks. */
 int gdy_abi_version(void);
 
 /* Number of usable sm_100 devices (0 if none or no driver): replaces cudaGetDeviceCount in
@@ -50,7 +56,8 @@ int gdy_device_count(void);
 /* ---- lifetime ------------------------------------------------------------------------------
  * Replaces Hermite4GPU::Hermite4GPU / alloc_arrays_device / ~Hermite4GPU
  * (reference: src/include/gpu/Hermite4GPU.cu:43-194).
- *   n       particle count
+ *   n       particle count, 1 <= n <= GDY_MAX_N (2^26 - 1: the index range the warp force kernel is built for;
+ *           larger n is refused with GDY_ERR_INVALID rather than computed wrongly)
  *   e2      softening squared, as NbodySystem computes it (float product widened,
  *           reference: src/include/NbodySystem.cpp:50)
  *   eta     accuracy parameter, FLOAT as in the reference (src/include/NbodySystem.hpp:67)
@@ -231,6 +238,14 @@ int gdy_set_tuning(gdy_ctx *ctx, int variant, int jsplit);
  * nact_max: 0 = off, < 0 = default, at most 2048.  Sharded contexts need gdy_peer_attach first. */
 int gdy_set_persist(gdy_ctx *ctx, int nact_max);
 int gdy_persist_stats(const gdy_ctx *ctx, uint64_t *launches_out, uint64_t *steps_out);
+/* Can the persistent kernel serve this context?  Returns 0 = switched off (gdy_set_persist(ctx, 0)), 1 = yes,
+ * 2 = NO: a CTA's slice of the predicted set (7 doubles per particle of the j-shard / number of SMs) plus its slice of
+ * t+dt (1 double per particle of ALL n / number of SMs) plus ~70 KB of fixed tables exceed the 227 KB of shared memory
+ * of an SM — above roughly 373 000 particles on one 148-SM GPU (N = 512k or 1M on one GPU; N = 1M fits from four GPUs
+ * on).  Such a context is NOT an error: gdy_run steps its small blocks through the per-hook kernels (about 50 us
+ * instead of 15 us per small block step), gdy_persist_stats stays at 0, and this call is how a driver finds out.
+ * smem_need_out / smem_max_out (may be NULL): bytes needed per CTA and the device's limit.  Negative = gdy_status. */
+int gdy_persist_state(gdy_ctx *ctx, uint32_t *smem_need_out, uint32_t *smem_max_out);
 /* ns per phase of that kernel seen by CTA 0 (slots 0-8: load, publish, predict+scan, wait for the active particles,
  * pair sums, owners' correction, wait for the corrected, lists, exit; 12/13: summed exchange wait of the owner warps
  * and their count); all zero unless GDY_PERSIST_PROF=1 was in the environment at gdy_create (measurement aid). */

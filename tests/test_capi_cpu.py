@@ -35,7 +35,7 @@ def test_header_symbols_all_exported(lib):
 
 
 def test_abi_version(lib):
-    assert lib.gdy_abi_version() == 2
+    assert lib.gdy_abi_version() == 3
 
 
 def test_no_cpu_fallback(lib):
@@ -53,6 +53,9 @@ def test_bad_arguments_rejected_before_device_work(lib):
     h = capi._ctx()
     assert lib.gdy_create(C.byref(h), 0, 1e-8, C.c_float(0.01), 0) == capi.GDY_ERR_INVALID
     assert lib.gdy_create_sharded(C.byref(h), 16, 1e-8, C.c_float(0.01), 0, 2, 2, None) == capi.GDY_ERR_INVALID
+    # n above the force kernel's index range (2^26 - 1) is refused, not computed wrongly (round-2 advisor finding)
+    assert lib.gdy_create(C.byref(h), 1 << 26, 1e-8, C.c_float(0.01), 0) == capi.GDY_ERR_INVALID
+    assert b"GDY_MAX_N" in lib.gdy_last_error(None)
     assert lib.gdy_destroy(None) == 0
     assert lib.gdy_launch_count(None) == 0
     assert lib.gdy_sync(None) == capi.GDY_ERR_INVALID

@@ -165,6 +165,10 @@ def test_checkpoint_restart_continues_the_schedule_bit_for_bit(binary, tmp_path,
     assert p.returncode != 0 and "already at or past" in p.stderr
     p = subprocess.run(common + ["-t", "0.5", "--restart", "./input.dat"], cwd=b, capture_output=True, text=True)
     assert p.returncode != 0 and "not a gravidy-b200 checkpoint" in p.stderr
+    # a checkpoint of an earlier layout is named as such (round-2 advisor finding: it used to be "not a checkpoint")
+    (b / "v1.ckpt").write_bytes(b"GDYCKPT1" + bytes(4096))
+    p = subprocess.run(common + ["-t", "0.5", "--restart", "./v1.ckpt"], cwd=b, capture_output=True, text=True)
+    assert p.returncode != 0 and "format version 1" in p.stderr and "reads version 2" in p.stderr
 
 
 def _gpu_count():

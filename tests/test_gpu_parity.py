@@ -279,6 +279,29 @@ def test_persistent_launch_may_outlast_the_watchdog(H, monkeypatch):
     assert np.array_equal(tn, tn2) and np.array_equal(ti, ti2) and st.atime == st2.atime
 
 
+def test_persist_state_reports_when_the_slices_do_not_fit(H):
+    """Above ~373k particles per GPU the persistent kernel's per-CTA slices exceed an SM's shared memory and gdy_run
+    quietly keeps to the per-hook kernels; gdy_persist_state is how a driver learns that (round-2 advisor finding)."""
+    m, r, v = plummer(4096, seed=default_seed(4096))
+    h = H(m, r, v)
+    state, need, lim = h.persist_state()
+    assert state == 1 and 0 < need <= lim
+    h.set_persist(0)
+    assert h.persist_state()[0] == 0
+    h.close()
+    n = 400_000
+    m, r, v = plummer(n, seed=7)
+    h = H(m, r, v)
+    state, need, lim = h.persist_state()
+    assert state == 2 and need > lim
+    h.init_acc_jrk()
+    atime = h.init_dt(0.0)
+    st, tn, ti = h.run(atime, 1e9, max_steps=40, trace_cap=40)
+    assert st.iterations == 40 and int(tn.min()) <= 512          # small blocks were stepped ...
+    assert h.persist_stats() == (0, 0) and h.persist_state()[0] == 2   # ... by the per-hook kernels
+    h.close()
+
+
 # ---- integration to t = 1 (BASELINE configs[0]) ------------------------------------------------------
 def test_run_n1024_to_t1_vs_reference_fixture(H, golden_dir):
     g = _load(golden_dir, "plummer_n1024_t1_eps1e-2")
