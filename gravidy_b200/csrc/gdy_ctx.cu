@@ -397,7 +397,7 @@ extern "C" int gdy_create_sharded(gdy_ctx **out, uint32_t n, double e2, float et
             if (fut.wait_for(std::chrono::milliseconds(tmo)) != std::future_status::ready)
             {
                 rc = fail(c, GDY_ERR_NCCL, "ncclCommInitRank: rank %d of %d waited %ld ms for the other ranks (a rank is missing or "
-                          "holds a different unique id)", rank, world, tmo);
+                          "holds a different unique id); the process must exit now: the init thread cannot be cancelled", rank, world, tmo);
                 break;
             }
             if (job->res != ncclSuccess) { rc = fail(c, GDY_ERR_NCCL, "ncclCommInitRank: %s", g_nccl.GetErrorString(job->res)); break; }

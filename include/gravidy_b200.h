@@ -72,7 +72,11 @@ int gdy_create(gdy_ctx **out, uint32_t n, double e2, float eta, int device);
  * caller (MPI, torch.distributed, a file, ...).  world == 1 ignores it (may be NULL).
  * Collective: returns when all `world` ranks have called it; a rank that waits longer than
  * GDY_NCCL_INIT_TIMEOUT_MS (environment, default 120000) for the others gets GDY_ERR_NCCL instead of
- * hanging (the reference reports and exits: src/include/gpu/Hermite4GPU.cuh:43-50). */
+ * hanging (the reference reports and exits: src/include/gpu/Hermite4GPU.cuh:43-50).
+ * After that timeout error the PROCESS MUST EXIT (the reference's convention): the helper thread that runs
+ * ncclCommInitRank cannot be cancelled and stays blocked inside NCCL, bound to the device; if the missing rank turns
+ * up later it completes a communicator nobody owns, and a second gdy_create_sharded with the same id would race with
+ * it.  Do not retry in the same process. */
 int gdy_create_sharded(gdy_ctx **out, uint32_t n, double e2, float eta, int device, int rank,
                        int world, const uint8_t *nccl_uid);
 /* world > 1 with nccl_uid == NULL makes a LOGICAL shard: no communicator, force results are this
