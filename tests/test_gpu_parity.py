@@ -434,3 +434,54 @@ def test_full_size_properties(H, O, n):
     if n <= 65536:
         e, ek, ep = h.get_energy()
         assert abs(e + 0.25) < 0.02 and abs(ek / abs(ep) - 0.5) < 0.03
+
+
+# ---- the block-timestep schedule at BASELINE sizes, against the reference loop on the host cores --------------------
+@pytest.mark.parametrize("n,spectrum", [(65536, "salpeter"), (262144, "equal")])
+def test_first_block_steps_match_the_reference_loop_at_baseline_sizes(H, O, n, spectrum):
+    """BASELINE configs 3 (N = 64k, Salpeter masses: small active blocks, j-split regime) and 4 (N = 256k) at their
+    real size: the first block steps of gdy_run against the reference's own loop body
+    (src/include/cpu/Hermite4CPU_integration.cpp:81-124 with Hermite4CPU::update_acc_jrk, src/include/cpu/
+    Hermite4CPU.cpp:309-336; oracle/_ref when built, else the C port) started from the same forces and timesteps.
+    Active-set sizes, block times and every particle's t and dt are BIT-EQUAL; positions and velocities agree to the
+    force tolerance.  Bounded to about 2e10 pair interactions of CPU work (about ten seconds on 16 cores)."""
+    m, r, v = plummer(n, seed=default_seed(n), mass_spectrum=spectrum)
+    h = H(m, r, v)
+    h.init_acc_jrk()
+    atime = h.init_dt(0.0)
+    start = h.get_state("f6", "t", "dt")
+    # forces of the starting state: a random subset against the oracle's update_acc_jrk
+    o = O.best_oracle(m, r, v)
+    o.set_threads(os.cpu_count() or 1)
+    rng = np.random.default_rng(3)
+    move = np.sort(rng.choice(n, size=64, replace=False)).astype(np.uint32)
+    o.timed_update(move)
+    ea, ej = rel_err(start["f6"][move], o.get_state("f6")["f6"][move])
+    assert ea < FORCE_RTOL and ej < FORCE_RTOL, (ea, ej)
+    # the GPU's first block steps, then as many of them on the CPU as the pair budget allows
+    cap = 400
+    st, tn, ti = h.run(atime, 1e9, max_steps=cap, trace_cap=cap)
+    cum = np.cumsum(tn.astype(np.float64) * n)
+    k = int(max(8, np.searchsorted(cum, 2e10)))
+    k = min(k, cap)
+    h.close()
+    h = H(m, r, v)
+    h.upload_forces(start["f6"]); h.upload_times(start["t"], start["dt"])
+    sg, tng, tig = h.run(atime, 1e9, max_steps=k, trace_cap=k)
+    o.set_state(f6=start["f6"], t=start["t"], dt=start["dt"])
+    so, tno, tio = o.run(atime, 1e9, max_steps=k, trace_cap=k)
+    assert np.array_equal(tng, tn[:k]) and np.array_equal(tig, ti[:k])      # the restarted run repeats the first one
+    assert sg.iterations == so.iterations == k
+    assert np.array_equal(tng, tno) and np.array_equal(tig, tio), "active-set sizes / block times differ from the reference loop"
+    assert sg.atime == so.atime and sg.interactions == so.interactions
+    a, b = h.get_state("t", "dt", "r4", "v4", "f6"), o.get_state("t", "dt", "r4", "v4", "f6")
+    assert np.array_equal(a["t"], b["t"]) and np.array_equal(a["dt"], b["dt"])
+    np.testing.assert_allclose(a["r4"], b["r4"], rtol=0, atol=1e-12)
+    np.testing.assert_allclose(a["v4"], b["v4"], rtol=0, atol=1e-12)
+    moved = a["t"] > 0
+    assert moved.any()
+    ea, ej = rel_err(a["f6"][moved], b["f6"][moved])
+    assert ea < 1e-10 and ej < 1e-10, (ea, ej)    # forces at slightly different (1e-16) positions after k steps
+    print(f"n={n} {spectrum}: {k} block steps, {int(cum[k - 1]):d} pairs, nact {int(tno.min())}..{int(tno.max())}, oracle {o.kind}")
+    o.close()
+
