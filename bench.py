@@ -43,6 +43,29 @@ UNIT = "GFLOP/s"
 NCU_DRAM_BYTES_PER_LAUNCH = 14886912 + 2654720   # profiles/r02_force_warp_ncu.md (capture r02u)
 
 
+def workload_name(n):
+    """config.workload, the same string in both arms (the driver compares them)."""
+    return f"full-active acc+jerk sweep (init_acc_jrk force evaluation), Plummer N={n}, eps=1e-4, self pair counted"
+
+
+def physical_cores():
+    """Physical cores of this box (distinct (package, core) pairs of /proc/cpuinfo); None if it cannot be told."""
+    try:
+        seen, phys, core = set(), None, None
+        for ln in open("/proc/cpuinfo"):
+            if ln.startswith("physical id"):
+                phys = ln.split(":")[1].strip()
+            elif ln.startswith("core id"):
+                core = ln.split(":")[1].strip()
+            elif not ln.strip():
+                if phys is not None and core is not None:
+                    seen.add((phys, core))
+                phys = core = None
+        return len(seen) or None
+    except OSError:
+        return None
+
+
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -96,10 +119,12 @@ def run_reference(args, m, r, v):
     per_step = max(args.cpu_seconds / max(args.steps, 1), 2.0)
     for _ in range(args.warmup):
         cpu_force_rate(m, r, v, 0.5)
-    rates, info = [], None
+    rates, step_s, info = [], [], None
     t0 = time.perf_counter()
     for _ in range(args.steps):
+        ts = time.perf_counter()
         rate, info = cpu_force_rate(m, r, v, per_step)
+        step_s.append(time.perf_counter() - ts)
         rates.append(rate)
     wall = time.perf_counter() - t0
     rate = float(np.mean(rates))
@@ -109,13 +134,15 @@ def run_reference(args, m, r, v):
     line = {
         "impl": "reference", "metric": METRIC, "value": gflops, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": n * float(n) / rate * 1e3,
+        # a step of this arm IS the bounded sample (task contract): its measured duration, not a scaled one
+        "ms_per_step": float(np.mean(step_s)) * 1e3,
+        "ms_per_full_sweep_scaled": n * float(n) / rate * 1e3,
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
         "data": "synthetic",
-        "config": {"workload": f"full-active acc+jerk sweep, Plummer N={n}, eps=1e-4", "n": n},
+        "config": {"workload": workload_name(n), "n": n},
         "pairs_per_s": rate,
-        "cpu_baseline": {"value": gflops, "unit": UNIT, "cores": info["cores"], "kind": info["kind"],
-                         "sample": sample},
+        "cpu_baseline": {"value": gflops, "unit": UNIT, "cores": info["cores"], "physical_cores": physical_cores(),
+                         "kind": info["kind"], "sample": sample},
         "e2e": {"value": gflops, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "wall_s": wall,
     }
@@ -498,7 +525,7 @@ def run_b200(args, m, r, v):
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         crate, info = cpu_force_rate(m, r, v, args.cpu_seconds)
         cpu = {"value": crate * FLOP_PER_PAIR / 1e9, "unit": UNIT, "cores": info["cores"],
-               "kind": info["kind"],
+               "physical_cores": physical_cores(), "kind": info["kind"],
                "sample": f"update_acc_jrk-style sweep of {info['nact']} of {n} i-particles x {n} j "
                          f"({info['seconds']:.1f} s), scaled to the full N^2"}
         if integ is not None and args.cpu_loop_steps > 0:
@@ -540,8 +567,7 @@ def run_b200(args, m, r, v):
             "metric": METRIC, "value": gflops, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": f"full-active acc+jerk sweep (init_acc_jrk force evaluation), Plummer "
-                                   f"N={n}, eps=1e-4, self pair counted", "n": n,
+            "config": {"workload": workload_name(n), "n": n,
                        "sharding": f"j-sharded x{world}, NCCL allreduce of partial forces" if world > 1 else "1 GPU",
                        "l2": "flushed between timed iterations (256 MiB write)"},
             "pairs_per_s": rate,

@@ -112,6 +112,33 @@ PY
           python /tmp/ncu_energy.py > $O/${TAG}_ncu_$K.log 2>&1
         echo "[$st] $K rc=$? $(tail -2 $O/${TAG}_ncu_$K.log | tr '\n' ' ')"
       done;;
+    ncu_step)
+      # ncu --set full of the memory-bound step kernels at N = 256k (predictor, corrector, scheduler passes): the hook
+      # sequence of a few block steps with the persistent kernel off; the program runs once WITHOUT ncu first
+      cat > /tmp/ncu_step.py <<'PY'
+import sys; sys.path.insert(0, ".")
+from gravidy_b200.hermite4 import Hermite4B200
+from gravidy_b200.plummer import plummer, default_seed
+n = 262144
+m, r, v = plummer(n, seed=default_seed(n))
+h = Hermite4B200(m, r, v, softening=1e-4, eta=0.01, device=0)
+h.set_persist(0)
+h.init_acc_jrk(); at = h.init_dt(0.0)
+for s in range(12):
+    nact = h.find_particles_to_move(at)
+    h.save_old_acc_jrk(nact); h.predicted_pos_vel(at); h.update_acc_jrk(nact); h.correction_pos_vel(at, nact)
+    at = h.next_integration_time()
+print("steps ok, last nact", nact, "predict ms", h.predict_timed(at))
+PY
+      timeout 300 python /tmp/ncu_step.py > $O/${TAG}_ncu_step_plain.log 2>&1 && \
+      timeout 900 ncu --set full --clock-control none --import-source on -k regex:"k_predict|k_correct|k_min_time|k_sched_count|k_sched_write|k_save_old" \
+        --launch-skip 6 -c 12 -f -o $O/${TAG}_step_kernels python /tmp/ncu_step.py > $O/${TAG}_ncu_step.log 2>&1
+      echo "[$st] rc=$? $(tail -2 $O/${TAG}_ncu_step.log | tr '\n' ' ')";;
+    hostprog)
+      # hostprog:<n>:<tend>:<gpus>[:extra args]  the product binary timed from the outside (tools/host_program_run.py)
+      timeout 1500 python tools/host_program_run.py --particles ${a1:-16384} --tend ${a2:-1} --gpus ${a3:-1} ${a4:-} \
+        >> $O/${TAG}_hostprog.jsonl 2> $O/${TAG}_hostprog.err
+      echo "[$st] rc=$? $(tail -1 $O/${TAG}_hostprog.jsonl | cut -c1-700)";;
     lab)
       # lab[:nacts]: every library build under gravidy_b200/lab/ against the production library: forces bit for bit
       # (tools/lab/force_cmp.sh) and the big-block rates (tools/sweep_big.py)
