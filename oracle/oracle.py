@@ -273,6 +273,30 @@ class RefOracle(_Base):
     def J(self):
         return int(self.lib.gref_J())
 
+    def lagrange_radii(self):
+        """NbodyUtils::lagrange_radii of the reference on the current positions: the six Lagrange radii
+        (1, 5, 10, 20, 50, 75 % of the mass; reference: src/include/utils/NbodyUtils.cpp:262-328)."""
+        self.lib.gref_lagrange_radii.argtypes = [C.c_void_p, _dp]
+        self.lib.gref_lagrange_radii.restype = None
+        out = np.zeros(6)
+        self.lib.gref_lagrange_radii(self.h, _ptr(out, _dp))
+        return out
+
+    def core_and_relaxation(self):
+        """(r_core, t_rlx, r_hm): get_core_radius + get_half_mass_relaxation_time of the reference
+        (src/include/utils/NbodyUtils.cpp:113-160, 223-258) around the density centre of the last call."""
+        self.lib.gref_core_and_relaxation.argtypes = [C.c_void_p, _dp]
+        self.lib.gref_core_and_relaxation.restype = None
+        out = np.zeros(3)
+        self.lib.gref_core_and_relaxation(self.h, _ptr(out, _dp))
+        return tuple(out)
+
+    def pad_layers(self):
+        """Room for the reference's -l overrun (see oracle/ref_harness.cpp: gref_pad_layers); call before integration()."""
+        self.lib.gref_pad_layers.argtypes = [C.c_void_p]
+        self.lib.gref_pad_layers.restype = None
+        self.lib.gref_pad_layers(self.h)
+
     def set_print_options(self, print_all=False, print_lagrange=False):
         self.lib.gref_set_print_options.argtypes = [C.c_void_p, C.c_int, C.c_int]
         self.lib.gref_set_print_options(self.h, int(print_all), int(print_lagrange))

@@ -150,6 +150,30 @@ void gref_set_print_options(gref *g, int print_all, int print_lagrange)
     g->ns->ops.print_lagrange = print_lagrange;
 }
 
+// -l in the reference writes past the end of layers_radii: get_layers (NbodyUtils.cpp:300-328) keeps counting layers
+// after the sixth, and the vector holds six (NbodyUtils.cpp:46).  The member is public, so the harness gives it room
+// for one entry per particle BEFORE the run; the reference's code itself is untouched and the logger prints the first
+// six entries only (Logger.cpp:257-261).
+void gref_pad_layers(gref *g)
+{
+    g->nu->layers_radii.resize(g->ns->n + 16, 0.0);
+}
+// NbodyUtils::lagrange_radii (NbodyUtils.cpp:262-278) on the current positions: density centre, sorted radii, layers.
+void gref_lagrange_radii(gref *g, double *out6)
+{
+    gref_pad_layers(g);
+    g->nu->lagrange_radii();
+    for (int k = 0; k < 6; ++k) out6[k] = g->nu->layers_radii[k];
+}
+// get_core_radius (NbodyUtils.cpp:113-144) and get_half_mass_relaxation_time (:149-160, sets ns->r_hm) around the
+// density centre the previous call left in nu->cod.  out3 = {r_core, t_rlx, r_hm}.
+void gref_core_and_relaxation(gref *g, double *out3)
+{
+    out3[0] = g->nu->get_core_radius();
+    out3[1] = g->nu->get_half_mass_relaxation_time();
+    out3[2] = g->ns->r_hm;
+}
+
 // ---- state copy-out / copy-in (plain doubles; NULL pointers are skipped) -------------------
 // r4: n x {x,y,z,m}   v4: n x {x,y,z,0}   f6/old6: n x {a[3],a1[3]}   a2/a3: n x 3
 // p7: n x {r[3],v[3],m} with m widened from float       move: n x uint32

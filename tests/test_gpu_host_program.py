@@ -94,6 +94,16 @@ def test_lagrange_radii_and_resume(binary, tmp_path):
     assert len(radii) == 3 and all(r[0] == "01" and len(r) == 8 for r in radii)
     vals = np.array([[float(t) for t in r[2:]] for r in radii])
     assert (np.diff(vals, axis=1) >= 0).all() and (vals > 0).all()   # radii grow with the mass fraction
+    # against the file the unmodified reference driver writes with -l for the same run (tests/golden/
+    # make_golden_radii.py; NbodyUtils::lagrange_radii, reference: src/include/utils/NbodyUtils.cpp:262-328): same
+    # times, radii equal to the six printed decimals (one unit of the last digit for a rounding flip)
+    ref = [ln.split() for ln in open(os.path.join(ROOT, "tests", "golden", "ref_run_n64_radii", "run.out.radii")).read().splitlines()]
+    ref_vals = np.array([[float(t) for t in r[1:]] for r in ref[:3]])
+    got_vals = np.array([[float(t) for t in r[1:]] for r in radii])
+    assert np.array_equal(got_vals[:, 0], ref_vals[:, 0])
+    np.testing.assert_allclose(got_vals[:, 1:], ref_vals[:, 1:], rtol=0, atol=1.01e-6)
+    full = np.load(os.path.join(ROOT, "tests", "golden", "ref_run_n64_radii", "ref_radii.npz"))
+    np.testing.assert_allclose(got_vals[0, 1:], full["lagrange_t0"], rtol=0, atol=5.01e-7)   # t = 0: the rounded reference values
     # resume: needs a longer -t than the info file, restarts from the last snapshot
     p = subprocess.run([binary, "-r", "./input.dat.out.info", "-t", "0.25"], cwd=tmp_path,
                        capture_output=True, text=True, timeout=300)

@@ -112,3 +112,26 @@ def test_normalize_dt_edges():
     assert o.normalize_dt(old * 3, old, 3 * old) == old          # not commensurate: stays
     assert o.normalize_dt(1.0, dmax, 0.0) == dmax                # clamp
     assert o.normalize_dt(float("nan"), old, 0.0) == old         # NaN falls through
+
+
+def test_lagrange_radii_fixture_is_the_reference_output(golden_dir):
+    """tests/golden/ref_run_n64_radii (the reference driver's -l file and the t = 0 values in full precision) against
+    the reference compiled here: NbodyUtils::lagrange_radii / get_core_radius / get_half_mass_relaxation_time
+    (reference: src/include/utils/NbodyUtils.cpp:113-160, 223-328).  Skips where oracle/_ref is not built."""
+    from oracle import oracle as O
+    if not O.have_ref():
+        pytest.skip("oracle/_ref not built")
+    from gravidy_b200.plummer import plummer
+    m, r, v = plummer(64, seed=3)
+    o = O.RefOracle(m, r, v, softening=1e-4, eta=0.01)
+    o.set_threads(1)
+    lag = o.lagrange_radii()
+    core = o.core_and_relaxation()
+    o.close()
+    g = np.load(os.path.join(golden_dir, "ref_run_n64_radii", "ref_radii.npz"))
+    assert np.array_equal(lag, g["lagrange_t0"])
+    assert core == (float(g["r_core"]), float(g["t_rlx"]), float(g["r_hm"]))
+    assert (np.diff(lag) > 0).all()
+    row0 = open(os.path.join(golden_dir, "ref_run_n64_radii", "run.out.radii")).readline().split()
+    np.testing.assert_allclose([float(t) for t in row0[2:]], lag, rtol=0, atol=5.01e-7)
+
